@@ -1,0 +1,245 @@
+// api.cu -- C ABI (include/mpmk.h): context lifecycle, the substep driver (solver.py:27-52 order) and
+// CUDA-graph replay of constant-dt substep batches.
+#include "common.cuh"
+
+static int ceil_log2(uint64_t v) { int b = 0; while ((1ull << b) < v) ++b; return b; }
+
+extern "C" int mpmk_version(void) { return MPMK_VERSION; }
+
+extern "C" const char* mpmk_last_error(mpmk_ctx* ctx) { return ctx ? ctx->err : "null context"; }
+
+#define ALLOC0(ctx, ptr, bytes)                                        \
+    do {                                                               \
+        MPMK_CHECK(ctx, cudaMalloc((void**)&(ptr), (bytes)));          \
+        MPMK_CHECK(ctx, cudaMemset((ptr), 0, (bytes)));                \
+    } while (0)
+
+static int create_impl(mpmk_ctx* ctx, int device, int n_grid, double grid_extent, int64_t capacity) {
+    MPMK_CHECK(ctx, cudaSetDevice(device));
+    cudaDeviceProp prop;
+    MPMK_CHECK(ctx, cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) MPMK_FAIL(ctx, MPMK_ERR_INVALID, "libmpmk is built for sm_100a only (device is sm_%d%d)", prop.major, prop.minor);
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    ctx->n_grid = n_grid;
+    ctx->nt = (n_grid + MPMK_TILE - 1) / MPMK_TILE;
+    ctx->nb = (n_grid + 3) / 4;
+    ctx->dx = (float)(grid_extent / (double)n_grid);      // model.py:15
+    ctx->inv_dx = (float)((double)n_grid / grid_extent);  // model.py:16
+    ctx->capacity = capacity;
+    ctx->key_bits = 6 + ceil_log2((uint64_t)ctx->nt * ctx->nt * ctx->nt);
+    if (ctx->key_bits > 32) MPMK_FAIL(ctx, MPMK_ERR_INVALID, "grid too large for 32-bit keys");
+    const size_t cap = (size_t)(capacity > 0 ? capacity : 1);
+    ALLOC0(ctx, ctx->keys_alt, cap * 4);
+    ALLOC0(ctx, ctx->sorted_keys, cap * 4);
+    ALLOC0(ctx, ctx->perm, cap * 4);
+    ALLOC0(ctx, ctx->perm_alt, cap * 4);
+    ctx->n_sort_ctas_cap = div_up((int64_t)cap, MPMK_SORT_CHUNK);
+    ALLOC0(ctx, ctx->hist, (size_t)(1 << MPMK_MAX_RADIX_BITS) * ctx->n_sort_ctas_cap * 4);
+    ALLOC0(ctx, ctx->hist_tot, 1024 * 4);
+    const size_t ntiles = (size_t)ctx->nt * ctx->nt * ctx->nt;
+    ctx->items_cap = (int64_t)(cap / MPMK_ITEM_MAX + (cap < ntiles ? cap : ntiles) + 8);
+    ALLOC0(ctx, ctx->items, (size_t)ctx->items_cap * sizeof(uint4));
+    const size_t nblocks = (size_t)ctx->nb * ctx->nb * ctx->nb;
+    ALLOC0(ctx, ctx->block_stamp, nblocks * 4);
+    ALLOC0(ctx, ctx->block_list[0], nblocks * 4);
+    ALLOC0(ctx, ctx->block_list[1], nblocks * 4);
+    ALLOC0(ctx, ctx->block_count[0], 4);
+    ALLOC0(ctx, ctx->block_count[1], 4);
+    ALLOC0(ctx, ctx->counters, sizeof(DevCounters));
+    ALLOC0(ctx, ctx->dev_stamp, 4);
+    ctx->prm.alpha = 0.0f;
+    return 0;
+}
+
+extern "C" int mpmk_create(mpmk_ctx** out, int device, int n_grid, double grid_extent, int64_t capacity) {
+    if (!out || n_grid < 3 || grid_extent <= 0.0 || capacity < 0) return MPMK_ERR_INVALID;
+    mpmk_ctx* ctx = new mpmk_ctx();
+    memset(ctx, 0, sizeof(*ctx));
+    *out = ctx;  // returned even on failure so the caller can read the message, then destroy
+    return create_impl(ctx, device, n_grid, grid_extent, capacity);
+}
+
+extern "C" int mpmk_destroy(mpmk_ctx* ctx) {
+    if (!ctx) return 0;
+    for (int i = 0; i < ctx->n_graphs; ++i) cudaGraphExecDestroy(ctx->graphs[i].exec);
+    cudaFree(ctx->keys_alt); cudaFree(ctx->sorted_keys); cudaFree(ctx->perm); cudaFree(ctx->perm_alt);
+    cudaFree(ctx->hist); cudaFree(ctx->hist_tot); cudaFree(ctx->items); cudaFree(ctx->block_stamp);
+    cudaFree(ctx->block_list[0]); cudaFree(ctx->block_list[1]); cudaFree(ctx->block_count[0]); cudaFree(ctx->block_count[1]);
+    cudaFree(ctx->counters); cudaFree(ctx->dev_stamp);
+    delete ctx;
+    return 0;
+}
+
+static void drop_graphs(mpmk_ctx* ctx) {
+    for (int i = 0; i < ctx->n_graphs; ++i) cudaGraphExecDestroy(ctx->graphs[i].exec);
+    ctx->n_graphs = 0;
+}
+
+extern "C" int mpmk_bind(mpmk_ctx* ctx, const mpmk_bindings* b) {
+    if (!ctx || !b) return MPMK_ERR_INVALID;
+    for (int s = 0; s < 2; ++s) {
+        const mpmk_particle_set& p = b->set[s];
+        if (!p.xm || !p.vv || !p.c0 || !p.c1 || !p.cs || !p.s1 || !p.f0 || !p.f1 || !p.f2 || !p.meta)
+            MPMK_FAIL(ctx, MPMK_ERR_INVALID, "mpmk_bind: particle set %d has a null array", s);
+    }
+    if (!b->keys || !b->grid_in || !b->grid_out) MPMK_FAIL(ctx, MPMK_ERR_INVALID, "mpmk_bind: keys/grid_in/grid_out must be bound");
+    ctx->b = *b;
+    ctx->bound = true;
+    ctx->sorted_valid = false;
+    ctx->prepared = false;
+    ctx->ftrial_valid = false;
+    drop_graphs(ctx);
+    return 0;
+}
+
+extern "C" int mpmk_set_params(mpmk_ctx* ctx, const mpmk_params* p) {
+    if (!ctx || !p) return MPMK_ERR_INVALID;
+    ctx->prm = *p;
+    return 0;
+}
+
+extern "C" int mpmk_set_count(mpmk_ctx* ctx, int64_t n, int current_set) {
+    if (!ctx) return MPMK_ERR_INVALID;
+    if (n < 0 || n > ctx->capacity || (current_set != 0 && current_set != 1))
+        MPMK_FAIL(ctx, MPMK_ERR_INVALID, "mpmk_set_count: n=%lld capacity=%lld set=%d", (long long)n, (long long)ctx->capacity, current_set);
+    ctx->n = n;
+    ctx->cur = current_set;
+    ctx->sorted_valid = false;
+    ctx->prepared = false;
+    ctx->ftrial_valid = false;
+    return 0;
+}
+
+extern "C" int mpmk_current_set(mpmk_ctx* ctx) { return ctx ? ctx->cur : -1; }
+extern "C" int64_t mpmk_count(mpmk_ctx* ctx) { return ctx ? ctx->n : -1; }
+extern "C" int64_t mpmk_launch_count(mpmk_ctx* ctx) { return ctx ? ctx->launches : -1; }
+
+#define REQUIRE_BOUND(ctx)                                                        \
+    do {                                                                          \
+        if (!(ctx)) return MPMK_ERR_INVALID;                                      \
+        if (!(ctx)->bound) MPMK_FAIL(ctx, MPMK_ERR_STATE, "call mpmk_bind first"); \
+    } while (0)
+
+extern "C" int mpmk_compute_keys(mpmk_ctx* ctx, void* stream) {
+    REQUIRE_BOUND(ctx);
+    return mpmk_launch_keys(ctx, (cudaStream_t)stream);
+}
+extern "C" int mpmk_sort(mpmk_ctx* ctx, void* stream) {
+    REQUIRE_BOUND(ctx);
+    return mpmk_launch_sort(ctx, (cudaStream_t)stream);
+}
+extern "C" int mpmk_get_sort_result(mpmk_ctx* ctx, void* sorted_keys_dev, void* perm_dev, void* stream) {
+    REQUIRE_BOUND(ctx);
+    if (!ctx->sorted_valid) MPMK_FAIL(ctx, MPMK_ERR_STATE, "no valid sort result");
+    if (sorted_keys_dev) MPMK_CHECK(ctx, cudaMemcpyAsync(sorted_keys_dev, ctx->sorted_keys, ctx->n * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    if (perm_dev) MPMK_CHECK(ctx, cudaMemcpyAsync(perm_dev, ctx->perm, ctx->n * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return 0;
+}
+extern "C" int mpmk_prepare_grid(mpmk_ctx* ctx, void* stream) {
+    REQUIRE_BOUND(ctx);
+    return mpmk_launch_prepare(ctx, (cudaStream_t)stream);
+}
+extern "C" int mpmk_p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, void* stream) {
+    REQUIRE_BOUND(ctx);
+    return mpmk_launch_p2g(ctx, dt, ops, (cudaStream_t)stream);
+}
+extern "C" int mpmk_grid_update(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, void* stream) {
+    REQUIRE_BOUND(ctx);
+    return mpmk_launch_grid(ctx, dt, ops, (cudaStream_t)stream);
+}
+extern "C" int mpmk_g2p(mpmk_ctx* ctx, float dt, void* stream) {
+    REQUIRE_BOUND(ctx);
+    return mpmk_launch_g2p(ctx, dt, (cudaStream_t)stream);
+}
+
+static int substep_impl(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s) {
+    int rc;
+    if ((rc = mpmk_launch_sort(ctx, s))) return rc;
+    if ((rc = mpmk_launch_prepare(ctx, s))) return rc;
+    if ((rc = mpmk_launch_p2g(ctx, dt, ops, s))) return rc;
+    if ((rc = mpmk_launch_grid(ctx, dt, ops, s))) return rc;
+    return mpmk_launch_g2p(ctx, dt, s);
+}
+
+extern "C" int mpmk_substep(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, void* stream) {
+    REQUIRE_BOUND(ctx);
+    return substep_impl(ctx, dt, ops, (cudaStream_t)stream);
+}
+
+static bool same_bindings(const mpmk_bindings& a, const mpmk_bindings& b) { return memcmp(&a, &b, sizeof(a)) == 0; }
+
+extern "C" int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, int n_steps, void* stream) {
+    REQUIRE_BOUND(ctx);
+    if (n_steps <= 0) return 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    mpmk_substep_ops zero_ops;
+    memset(&zero_ops, 0, sizeof(zero_ops));
+    if (!ops) ops = &zero_ops;
+    const uint32_t user_flags = ctx->prm.flags;
+    // look for a captured graph with identical launch parameters
+    for (int i = 0; i < ctx->n_graphs; ++i) {
+        mpmk_ctx::GraphEntry& g = ctx->graphs[i];
+        if (g.n_steps == n_steps && g.dt == dt && g.cur == ctx->cur && g.cur_list == ctx->cur_list && g.flags == user_flags &&
+            g.n == ctx->n && memcmp(&g.ops, ops, sizeof(*ops)) == 0 && same_bindings(g.b, ctx->b)) {
+            MPMK_CHECK(ctx, cudaGraphLaunch(g.exec, s));
+            ctx->launches += 1;
+            ctx->cur = (ctx->cur + n_steps) & 1;
+            ctx->cur_list = (ctx->cur_list + n_steps) & 1;
+            ctx->ftrial_valid = (user_flags & MPMK_WRITE_FTRIAL) != 0;
+            ctx->sorted_valid = false;
+            ctx->prepared = false;
+            return 0;
+        }
+    }
+    // capture
+    mpmk_ctx::GraphEntry e;
+    memset(&e, 0, sizeof(e));
+    e.n_steps = n_steps; e.dt = dt; e.cur = ctx->cur; e.cur_list = ctx->cur_list; e.flags = user_flags; e.n = ctx->n;
+    e.ops = *ops; e.b = ctx->b;
+    const int64_t launches_before = ctx->launches;
+    MPMK_CHECK(ctx, cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+    int rc = 0;
+    for (int i = 0; i < n_steps && rc == 0; ++i) {
+        // F_trial is only consumed by export: store it on the last substep of the batch only
+        ctx->prm.flags = (i == n_steps - 1) ? user_flags : (user_flags & ~MPMK_WRITE_FTRIAL);
+        rc = substep_impl(ctx, dt, ops, s);
+    }
+    ctx->prm.flags = user_flags;
+    cudaGraph_t graph = nullptr;
+    cudaError_t ce = cudaStreamEndCapture(s, &graph);
+    if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+    MPMK_CHECK(ctx, ce);
+    cudaGraphExec_t exec = nullptr;
+    ce = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    MPMK_CHECK(ctx, ce);
+    e.exec = exec;
+    if (ctx->n_graphs == 4) {  // evict the oldest
+        cudaGraphExecDestroy(ctx->graphs[0].exec);
+        for (int i = 1; i < 4; ++i) ctx->graphs[i - 1] = ctx->graphs[i];
+        ctx->n_graphs = 3;
+    }
+    ctx->graphs[ctx->n_graphs++] = e;
+    ctx->launches = launches_before;  // captured launches did not run; the replay below is what executes
+    MPMK_CHECK(ctx, cudaGraphLaunch(exec, s));
+    ctx->launches += 1;
+    ctx->ftrial_valid = (user_flags & MPMK_WRITE_FTRIAL) != 0;
+    return 0;
+}
+
+extern "C" int mpmk_read_counters(mpmk_ctx* ctx, mpmk_counters* out, void* stream) {
+    REQUIRE_BOUND(ctx);
+    if (!out) return MPMK_ERR_INVALID;
+    DevCounters h;
+    uint32_t nb = 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    MPMK_CHECK(ctx, cudaMemcpyAsync(&h, ctx->counters, sizeof(h), cudaMemcpyDeviceToHost, s));
+    MPMK_CHECK(ctx, cudaMemcpyAsync(&nb, ctx->block_count[ctx->cur_list], 4, cudaMemcpyDeviceToHost, s));
+    MPMK_CHECK(ctx, cudaStreamSynchronize(s));
+    out->n_items = h.n_items;
+    out->n_active_blocks = nb;
+    out->n_tiles = h.n_tiles;
+    out->n_clamped = h.n_clamped;
+    return 0;
+}

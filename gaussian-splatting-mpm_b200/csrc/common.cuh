@@ -1,0 +1,133 @@
+// common.cuh -- context, launch helpers and small device utilities shared by the
+// libmpmk kernels.  sm_100a only; see include/mpmk.h for the ABI.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/mpmk.h"
+
+#define MPMK_TILE 4                 // cells per tile edge; a tile's stencil covers 6^3 nodes
+#define MPMK_TILE_NODES 216         // 6*6*6
+#define MPMK_ITEM_MAX 512           // particles per p2g/g2p work item (tile chunk)
+#define MPMK_SORT_CTA 256           // threads per sort CTA
+#define MPMK_SORT_ROUNDS 16         // keys per thread per sort CTA
+#define MPMK_SORT_CHUNK (MPMK_SORT_CTA * MPMK_SORT_ROUNDS)
+#define MPMK_MAX_RADIX_BITS 9
+
+struct DevCounters {
+    uint32_t n_items;
+    uint32_t n_active_blocks;
+    uint32_t n_tiles;
+    uint32_t n_clamped;
+    uint32_t p2g_cursor;   // dynamic work fetch
+    uint32_t g2p_cursor;
+    uint32_t pad[2];
+};
+
+struct mpmk_ctx {
+    int device;
+    int n_grid;        // nodes per edge
+    int nt;            // tiles per edge = ceil(n_grid/4)
+    int nb;            // node blocks per edge = ceil(n_grid/4)
+    float dx, inv_dx;
+    int64_t capacity;
+    int64_t n;         // live particles
+    int cur;           // which set holds the current state
+    int key_bits;
+    int sm_count;
+    mpmk_bindings b;
+    bool bound;
+    mpmk_params prm;
+    // scratch (library-owned)
+    uint32_t* keys_alt;      // sort ping-pong
+    uint32_t* sorted_keys;   // result of last sort
+    uint32_t* perm;          // result of last sort: physical slot of the r-th particle in sorted order
+    uint32_t* perm_alt;
+    uint32_t* hist;          // [digits][n_sort_ctas]
+    uint32_t* hist_tot;      // [digits]
+    int64_t n_sort_ctas_cap;
+    uint4* items;            // {begin, count, tile, 0}
+    int64_t items_cap;
+    uint32_t* block_stamp;   // [nb^3]
+    uint32_t* block_list[2]; // active node blocks: [cur_list] this substep, [1-cur_list] previous
+    uint32_t* block_count[2];// device scalars
+    int cur_list;
+    uint32_t* dev_stamp;     // device scalar: substep stamp for block_stamp (device-side so graphs replay correctly)
+    DevCounters* counters;
+    bool sorted_valid;       // sorted_keys/perm describe the current set
+    bool prepared;           // work list built for the current sort
+    bool ftrial_valid;
+    int64_t launches;
+    // CUDA graph cache for mpmk_substeps
+    struct GraphEntry {
+        cudaGraphExec_t exec;
+        float dt;
+        mpmk_substep_ops ops;
+        int n_steps;
+        int cur, cur_list;
+        uint32_t flags;
+        int64_t n;
+        mpmk_bindings b;
+    } graphs[4];
+    int n_graphs;
+    char err[512];
+};
+
+#define MPMK_CHECK(ctx, call)                                                                   \
+    do {                                                                                        \
+        cudaError_t e__ = (call);                                                               \
+        if (e__ != cudaSuccess) {                                                               \
+            snprintf((ctx)->err, sizeof((ctx)->err), "%s:%d %s: %s", __FILE__, __LINE__, #call, \
+                     cudaGetErrorString(e__));                                                  \
+            return (int)e__;                                                                    \
+        }                                                                                       \
+    } while (0)
+
+#define MPMK_FAIL(ctx, code, ...)                            \
+    do {                                                     \
+        snprintf((ctx)->err, sizeof((ctx)->err), __VA_ARGS__); \
+        return (code);                                       \
+    } while (0)
+
+#define MPMK_LAUNCH_CHECK(ctx)            \
+    do {                                  \
+        (ctx)->launches++;                \
+        MPMK_CHECK(ctx, cudaGetLastError()); \
+    } while (0)
+
+static inline int div_up(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+// ---- device helpers ---------------------------------------------------------------------
+__device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
+
+// 16-byte vector reduction to global memory (sm_90+): one L2 atomic transaction per node
+__device__ __forceinline__ void red_add_v4(float4* addr, float4 v) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z),
+                 "f"(v.w)
+                 : "memory");
+}
+
+// Base cell of a coordinate exactly as utils.py:94-95: (int)(x*inv_dx - 0.5), unfused, truncating;
+// clamped into the grid for memory safety (the reference has no clamp, quirk Q9).
+__device__ __forceinline__ int base_cell(float x, float inv_dx, int n_grid, bool& clamped) {
+    float gp = __fmul_rn(x, inv_dx);
+    int b = (int)__fsub_rn(gp, 0.5f);
+    if (b < 0) { b = 0; clamped = true; }
+    if (b > n_grid - 3) { b = n_grid - 3; clamped = true; }
+    return b;
+}
+
+__device__ __forceinline__ uint32_t make_key(int bx, int by, int bz, int nt) {
+    uint32_t tile = (uint32_t)(((bx >> 2) * nt + (by >> 2)) * nt + (bz >> 2));
+    return (tile << 6) | (uint32_t)(((bx & 3) << 4) | ((by & 3) << 2) | (bz & 3));
+}
+
+// internal launchers (one per translation unit)
+int mpmk_launch_keys(mpmk_ctx* ctx, cudaStream_t s);
+int mpmk_launch_sort(mpmk_ctx* ctx, cudaStream_t s);
+int mpmk_launch_prepare(mpmk_ctx* ctx, cudaStream_t s);
+int mpmk_launch_p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);
+int mpmk_launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);
+int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s);

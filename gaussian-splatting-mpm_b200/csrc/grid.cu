@@ -1,0 +1,75 @@
+// grid.cu -- K3: one fused pass over the node blocks p2g touched:
+//   utils.py:178-183 grid_normalization_and_gravity, then the registered grid operations in
+//   registration order (solver.py:41-46): boundary_conditions.py:23-27 BasicBC.apply (fixed_cube) and
+//   collider.py:13-44 MPM_Collider.collide.  Nodes p2g never touched keep v_out = 0, on which both
+//   operations are no-ops, so visiting only touched blocks is bit-equivalent to the dense passes.
+#include "common.cuh"
+
+struct GridOpsArg {
+    int n_ops;
+    mpmk_grid_op ops[MPMK_MAX_GRID_OPS];
+};
+
+__global__ void __launch_bounds__(256) k_grid(const float4* __restrict__ gin, float4* __restrict__ gout,
+                                              const uint32_t* __restrict__ list, const uint32_t* __restrict__ count,
+                                              int n, int nb, float dx, float dt, float gx, float gy, float gz,
+                                              const GridOpsArg ops) {
+    const int64_t total = (int64_t)(*count) * 64;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        uint32_t b = list[i >> 6];
+        int l = (int)(i & 63);
+        int bz = b % nb, by = (b / nb) % nb, bx = b / (nb * nb);
+        int ix = 4 * bx + (l >> 4), iy = 4 * by + ((l >> 2) & 3), iz = 4 * bz + (l & 3);
+        if (ix >= n || iy >= n || iz >= n) continue;
+        size_t node = ((size_t)ix * n + iy) * n + iz;
+        float4 m = gin[node];
+        float vx = 0.f, vy = 0.f, vz = 0.f;
+        if (m.w > 1e-15f) {
+            vx = __fdiv_rn(m.x, m.w) + dt * gx;
+            vy = __fdiv_rn(m.y, m.w) + dt * gy;
+            vz = __fdiv_rn(m.z, m.w) + dt * gz;
+        }
+        float px = (float)ix * dx, py = (float)iy * dx, pz = (float)iz * dx;
+        for (int o = 0; o < ops.n_ops; ++o) {
+            const mpmk_grid_op& op = ops.ops[o];
+            if (op.type == MPMK_OP_FIXED_CUBE) {
+                if (fabsf(px - op.a[0]) < op.b[0] && fabsf(py - op.a[1]) < op.b[1] && fabsf(pz - op.a[2]) < op.b[2]) {
+                    vx = 0.f; vy = 0.f; vz = 0.f;
+                }
+            } else {
+                float ox = px - op.a[0], oy = py - op.a[1], oz = pz - op.a[2];
+                float nx = op.b[0], ny = op.b[1], nz = op.b[2];
+                float dp = ox * nx + oy * ny + oz * nz;
+                if (dp < 0.f) {
+                    float nc = vx * nx + vy * ny + vz * nz;
+                    float mn = fminf(nc, 0.f);
+                    vx -= mn * nx; vy -= mn * ny; vz -= mn * nz;
+                    float len = sqrtf(vx * vx + vy * vy + vz * vz);
+                    if (nc < 0.f && len > 1e-20f) {
+                        float sc = fmaxf(0.f, len + nc * op.c);
+                        vx = sc * __fdiv_rn(vx, len); vy = sc * __fdiv_rn(vy, len); vz = sc * __fdiv_rn(vz, len);
+                    }
+                    vx *= 0.99f; vy *= 0.99f; vz *= 0.99f;  // collider.py:44, every node below the plane (Q4)
+                }
+            }
+        }
+        gout[node] = make_float4(vx, vy, vz, 0.f);
+    }
+}
+
+int mpmk_launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s) {
+    if (!ctx->prepared) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_grid_update: prepare_grid first");
+    GridOpsArg a;
+    a.n_ops = 0;
+    if (ops) {
+        if (ops->n_ops < 0 || ops->n_ops > MPMK_MAX_GRID_OPS) MPMK_FAIL(ctx, MPMK_ERR_INVALID, "n_ops out of range");
+        a.n_ops = ops->n_ops;
+        memcpy(a.ops, ops->ops, sizeof(mpmk_grid_op) * ops->n_ops);
+    }
+    k_grid<<<ctx->sm_count * 8, 256, 0, s>>>((const float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out,
+                                             ctx->block_list[ctx->cur_list], ctx->block_count[ctx->cur_list],
+                                             ctx->n_grid, ctx->nb, ctx->dx, dt, ctx->prm.gravity[0], ctx->prm.gravity[1],
+                                             ctx->prm.gravity[2], a);
+    MPMK_LAUNCH_CHECK(ctx);
+    return 0;
+}

@@ -1,0 +1,229 @@
+// p2g.cu -- K2: APIC particle-to-grid scatter (mpm_solver/utils.py:90-134) with the impulse
+// pre-process (boundary_conditions.py:41-45) folded into its prologue.
+//
+// One warp owns one work item = up to MPMK_ITEM_MAX consecutive sorted particles of one 4x4x4-cell
+// tile, and a private 6x6x6-node float4 tile {px,py,pz,m} in shared memory.  Per batch of 32 particles:
+//   phase A (lane = particle): coalesced float4 loads through the sort permutation, quadratic B-spline
+//     weights, and the tensor-product partial sums
+//         Y_ij = wy_j (wx_i (q + i A0) + dwx_i S0) + wx_i (wy_j j A1 + dwy_j S1),   R_k = wz_k k A2 + dwz_k S2
+//     with A = m C dx, S = -dt vol inv_dx stress, q = m v - A fx, staged in shared memory;
+//   phase B (lane = stencil node (i,j,k)): walks the batch in sorted order; node value
+//         wz_k Y_ij + (wx_i wy_j) R_k,  mass m wx_i wy_j wz_k
+//     accumulates in registers while consecutive particles share a cell (the groups
+//     __match_any_sync finds in phase A) and is added to the shared tile once per (cell run, node):
+//     no shared-memory atomics, every lane owns a distinct node.
+// The tile is flushed with one 16-byte red.global.add.v4.f32 per non-zero node.
+#include "common.cuh"
+
+#define P2G_WARPS 8
+#define P2G_REC_STRIDE 33  // float4 per record slot: 32 lanes + 1 pad (bank-conflict-free phase B reads)
+#define P2G_REC_SLOTS 12   // 9 x {Y_ij.xyz, wx_i wy_j} + 3 x {R_k.xyz, wz_k}
+
+struct __align__(16) P2GWarpSmem {
+    float4 rec[P2G_REC_SLOTS * P2G_REC_STRIDE];
+    float4 tile[MPMK_TILE_NODES];
+};
+
+struct P2GArgs {
+    const uint32_t* perm;
+    const uint32_t* skeys;
+    const float4 *xm, *vv, *c0, *c1, *cs, *s1;
+    const uint4* items;
+    DevCounters* cnt;
+    float4* grid_in;
+    int n_grid, nt;
+    float dx, inv_dx, dt;
+    int n_imp;
+    mpmk_impulse imp[MPMK_MAX_IMPULSES];
+};
+
+__global__ void __launch_bounds__(P2G_WARPS * 32, 2) k_p2g(const P2GArgs a) {
+    extern __shared__ float4 smem_raw[];
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    P2GWarpSmem& S = reinterpret_cast<P2GWarpSmem*>(smem_raw)[warp];
+    const bool node_lane = lane < 27;
+    const int ni = node_lane ? lane / 9 : 0, nj = node_lane ? (lane / 3) % 3 : 0, nk = node_lane ? lane % 3 : 0;
+    const int nij = ni * 3 + nj;
+    const int noff = ni * 36 + nj * 6 + nk;
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = lane; i < MPMK_TILE_NODES; i += 32) S.tile[i] = zero4;
+    __syncwarp();
+    const uint32_t n_items = a.cnt->n_items;
+    const int n = a.n_grid;
+
+    while (true) {
+        uint32_t it = 0;
+        if (lane == 0) it = atomicAdd(&a.cnt->p2g_cursor, 1u);
+        it = __shfl_sync(0xffffffffu, it, 0);
+        if (it >= n_items) break;
+        const uint4 item = a.items[it];
+        const int tz = item.z % a.nt, ty = (item.z / a.nt) % a.nt, tx = item.z / (a.nt * a.nt);
+        int cur_cell = -1;
+        float4 acc = zero4;
+
+        for (uint32_t b0 = 0; b0 < item.y; b0 += 32) {
+            const int nbatch = min(32u, item.y - b0);
+            int my_cell = 0;
+            float my_m = 0.f;
+            // ---------------- phase A: lane = particle ----------------
+            if (lane < nbatch) {
+                const uint32_t r = item.x + b0 + lane;
+                const uint32_t p = a.perm[r];
+                const uint32_t key = a.skeys[r];
+                const float4 X = ldg4(a.xm + p), V = ldg4(a.vv + p), C0 = ldg4(a.c0 + p), C1 = ldg4(a.c1 + p),
+                             CS = ldg4(a.cs + p), S1 = ldg4(a.s1 + p);
+                my_cell = key & 63;
+                const int lx = my_cell >> 4, ly = (my_cell >> 2) & 3, lz = my_cell & 3;
+                const float m = X.w, vol = S1.w;
+                my_m = m;
+                float vx = V.x, vy = V.y, vz = V.z;
+                for (int q = 0; q < a.n_imp; ++q) {
+                    const mpmk_impulse& im = a.imp[q];
+                    if (fabsf(X.x - im.center[0]) < im.size[0] && fabsf(X.y - im.center[1]) < im.size[1] &&
+                        fabsf(X.z - im.center[2]) < im.size[2]) {
+                        vx = vx + __fdiv_rn(im.force[0], m) * im.substep_dt;
+                        vy = vy + __fdiv_rn(im.force[1], m) * im.substep_dt;
+                        vz = vz + __fdiv_rn(im.force[2], m) * im.substep_dt;
+                    }
+                }
+                const float fx = __fmul_rn(X.x, a.inv_dx) - (float)(4 * tx + lx);
+                const float fy = __fmul_rn(X.y, a.inv_dx) - (float)(4 * ty + ly);
+                const float fz = __fmul_rn(X.z, a.inv_dx) - (float)(4 * tz + lz);
+                float wx[3], wy[3], wz[3], dwx[3], dwy[3], dwz[3];
+                {
+                    float wa = 1.5f - fx, wb = fx - 1.0f, wc = fx - 0.5f;
+                    wx[0] = wa * wa * 0.5f; wx[1] = 0.75f - wb * wb; wx[2] = wc * wc * 0.5f;
+                    dwx[0] = fx - 1.5f; dwx[1] = -2.0f * (fx - 1.0f); dwx[2] = fx - 0.5f;
+                    wa = 1.5f - fy; wb = fy - 1.0f; wc = fy - 0.5f;
+                    wy[0] = wa * wa * 0.5f; wy[1] = 0.75f - wb * wb; wy[2] = wc * wc * 0.5f;
+                    dwy[0] = fy - 1.5f; dwy[1] = -2.0f * (fy - 1.0f); dwy[2] = fy - 0.5f;
+                    wa = 1.5f - fz; wb = fz - 1.0f; wc = fz - 0.5f;
+                    wz[0] = wa * wa * 0.5f; wz[1] = 0.75f - wb * wb; wz[2] = wc * wc * 0.5f;
+                    dwz[0] = fz - 1.5f; dwz[1] = -2.0f * (fz - 1.0f); dwz[2] = fz - 0.5f;
+                }
+                // A = m C dx (columns A0,A1,A2), S = -dt vol inv_dx stress (symmetric), q = m v - A f
+                const float mdx = m * a.dx;
+                const float A00 = mdx * C0.x, A01 = mdx * C0.y, A02 = mdx * C0.z;
+                const float A10 = mdx * C0.w, A11 = mdx * C1.x, A12 = mdx * C1.y;
+                const float A20 = mdx * C1.z, A21 = mdx * C1.w, A22 = mdx * CS.x;
+                const float sc = -a.dt * vol * a.inv_dx;
+                const float S00 = sc * CS.y, S01 = sc * CS.z, S02 = sc * CS.w, S11 = sc * S1.x, S12 = sc * S1.y, S22 = sc * S1.z;
+                const float q0 = m * vx - (A00 * fx + A01 * fy + A02 * fz);
+                const float q1 = m * vy - (A10 * fx + A11 * fy + A12 * fz);
+                const float q2 = m * vz - (A20 * fx + A21 * fy + A22 * fz);
+                float T0[3], T1[3], T2[3];
+#pragma unroll
+                for (int j = 0; j < 3; ++j) {
+                    const float wj = wy[j] * (float)j;
+                    T0[j] = wj * A01 + dwy[j] * S01;
+                    T1[j] = wj * A11 + dwy[j] * S11;
+                    T2[j] = wj * A21 + dwy[j] * S12;
+                }
+#pragma unroll
+                for (int i = 0; i < 3; ++i) {
+                    const float fi = (float)i;
+                    const float X0 = wx[i] * (q0 + fi * A00) + dwx[i] * S00;
+                    const float X1 = wx[i] * (q1 + fi * A10) + dwx[i] * S01;
+                    const float X2 = wx[i] * (q2 + fi * A20) + dwx[i] * S02;
+#pragma unroll
+                    for (int j = 0; j < 3; ++j) {
+                        float4 yw;
+                        yw.x = wy[j] * X0 + wx[i] * T0[j];
+                        yw.y = wy[j] * X1 + wx[i] * T1[j];
+                        yw.z = wy[j] * X2 + wx[i] * T2[j];
+                        yw.w = wx[i] * wy[j];
+                        S.rec[(i * 3 + j) * P2G_REC_STRIDE + lane] = yw;
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    const float wk = wz[k] * (float)k;
+                    float4 rw;
+                    rw.x = wk * A02 + dwz[k] * S02;
+                    rw.y = wk * A12 + dwz[k] * S12;
+                    rw.z = wk * A22 + dwz[k] * S22;
+                    rw.w = wz[k];
+                    S.rec[(9 + k) * P2G_REC_STRIDE + lane] = rw;
+                }
+            }
+            __syncwarp();
+            // ---------------- phase B: lane = stencil node ----------------
+            const float4* recY = S.rec + nij * P2G_REC_STRIDE;
+            const float4* recR = S.rec + (9 + nk) * P2G_REC_STRIDE;
+#pragma unroll 4
+            for (int l = 0; l < nbatch; ++l) {
+                const int cell = __shfl_sync(0xffffffffu, my_cell, l);
+                const float m = __shfl_sync(0xffffffffu, my_m, l);
+                if (cell != cur_cell) {
+                    if (cur_cell >= 0) {
+                        __syncwarp();
+                        if (node_lane) {
+                            const int nd = (cur_cell >> 4) * 36 + ((cur_cell >> 2) & 3) * 6 + (cur_cell & 3) + noff;
+                            float4 t = S.tile[nd];
+                            t.x += acc.x; t.y += acc.y; t.z += acc.z; t.w += acc.w;
+                            S.tile[nd] = t;
+                        }
+                    }
+                    acc = zero4;
+                    cur_cell = cell;
+                }
+                const float4 yw = recY[l];
+                const float4 rw = recR[l];
+                acc.x += rw.w * yw.x + yw.w * rw.x;
+                acc.y += rw.w * yw.y + yw.w * rw.y;
+                acc.z += rw.w * yw.z + yw.w * rw.z;
+                acc.w += m * (yw.w * rw.w);
+            }
+            __syncwarp();
+        }
+        // last cell run -> tile
+        if (cur_cell >= 0 && node_lane) {
+            const int nd = (cur_cell >> 4) * 36 + ((cur_cell >> 2) & 3) * 6 + (cur_cell & 3) + noff;
+            float4 t = S.tile[nd];
+            t.x += acc.x; t.y += acc.y; t.z += acc.z; t.w += acc.w;
+            S.tile[nd] = t;
+        }
+        __syncwarp();
+        // tile -> global grid (16-byte vector reductions), and reset for the next item
+        for (int i = lane; i < MPMK_TILE_NODES; i += 32) {
+            const float4 t = S.tile[i];
+            S.tile[i] = zero4;
+            if (t.x != 0.f || t.y != 0.f || t.z != 0.f || t.w != 0.f) {
+                const int gx = 4 * tx + i / 36, gy = 4 * ty + (i / 6) % 6, gz = 4 * tz + i % 6;
+                if (gx < n && gy < n && gz < n) red_add_v4(a.grid_in + (((size_t)gx * n + gy) * n + gz), t);
+            }
+        }
+        __syncwarp();
+    }
+}
+
+int mpmk_launch_p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s) {
+    if (!ctx->prepared) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_p2g: prepare_grid first");
+    if (ctx->n == 0) return 0;
+    const mpmk_particle_set& ps = ctx->b.set[ctx->cur];
+    P2GArgs a;
+    a.perm = ctx->perm; a.skeys = ctx->sorted_keys;
+    a.xm = (const float4*)ps.xm; a.vv = (const float4*)ps.vv; a.c0 = (const float4*)ps.c0;
+    a.c1 = (const float4*)ps.c1; a.cs = (const float4*)ps.cs; a.s1 = (const float4*)ps.s1;
+    a.items = ctx->items; a.cnt = ctx->counters; a.grid_in = (float4*)ctx->b.grid_in;
+    a.n_grid = ctx->n_grid; a.nt = ctx->nt; a.dx = ctx->dx; a.inv_dx = ctx->inv_dx; a.dt = dt;
+    a.n_imp = 0;
+    if (ops) {
+        if (ops->n_impulses < 0 || ops->n_impulses > MPMK_MAX_IMPULSES) MPMK_FAIL(ctx, MPMK_ERR_INVALID, "n_impulses out of range");
+        a.n_imp = ops->n_impulses;
+        memcpy(a.imp, ops->impulses, sizeof(mpmk_impulse) * ops->n_impulses);
+    }
+    static bool attr_set = false;
+    const int smem = (int)sizeof(P2GWarpSmem) * P2G_WARPS;
+    if (!attr_set) {
+        MPMK_CHECK(ctx, cudaFuncSetAttribute(k_p2g, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_set = true;
+    }
+    // persistent grid: 2 CTAs per SM, warps fetch items dynamically
+    int64_t want = (ctx->n / 32 + P2G_WARPS - 1) / P2G_WARPS + 1;
+    int grid = (int)(want < (int64_t)ctx->sm_count * 2 ? want : (int64_t)ctx->sm_count * 2);
+    k_p2g<<<grid, P2G_WARPS * 32, smem, s>>>(a);
+    MPMK_LAUNCH_CHECK(ctx);
+    return 0;
+}

@@ -1,0 +1,89 @@
+"""Deterministic synthetic particle clouds.
+
+A block of grid cells filled with `ppc` stratified-jittered particles per cell (for ppc=8: one per
+octant, uniform inside the octant), rigid spin about the block centre, random anisotropic
+covariances.  numpy only, so the same cloud feeds the CUDA solver and the CPU oracle.
+"""
+from __future__ import annotations
+
+import types
+
+import numpy as np
+
+SEED = 20240501
+
+WORKLOADS = {
+    # name: (n_grid, grid_extent, cells_lo, cells_n, dt)
+    "S-4M": (256, 2.0, (88, 88, 88), (80, 80, 80), 1e-4),            # N = 4,096,000
+    "S-32M": (512, 2.0, (176, 176, 176), (160, 160, 160), 5e-5),      # N = 32,768,000
+    "S-32M-bar": (512, 2.0, (32, 208, 208), (448, 96, 96), 5e-5),     # N = 33,030,144 (multi-GPU slabs)
+    "S-512K": (128, 2.0, (44, 44, 44), (40, 40, 40), 2e-4),           # N = 512,000 (tests)
+    "S-64K": (64, 2.0, (22, 22, 22), (20, 20, 20), 4e-4),             # N = 64,000 (tests)
+}
+
+
+def make_cloud(n_grid, grid_extent, cells_lo, cells_n, ppc=8, seed=SEED, omega=(0.0, 0.0, 2.0)):
+    """Returns dict(xyz[N,3], vel[N,3], cov[N,6], vol[N]) float32, particle-major over cells (x slowest)."""
+    rng = np.random.default_rng(seed)
+    dx = grid_extent / n_grid
+    cx, cy, cz = cells_n
+    ncell = cx * cy * cz
+    ii, jj, kk = np.meshgrid(np.arange(cx), np.arange(cy), np.arange(cz), indexing="ij")
+    cell = np.stack([ii.ravel(), jj.ravel(), kk.ravel()], axis=1).astype(np.float64) + np.asarray(cells_lo, np.float64)
+    if ppc == 8:
+        octant = np.array([[a, b, c] for a in (0, 1) for b in (0, 1) for c in (0, 1)], np.float64) * 0.5
+        jit = rng.random((ncell, 8, 3)) * 0.5
+        frac = octant[None, :, :] + jit
+    else:
+        frac = rng.random((ncell, ppc, 3))
+    # keep a small margin from cell faces so fp32 rounding cannot move a particle across a face at t=0
+    frac = np.clip(frac, 1e-3, 1.0 - 1e-3)
+    xyz = ((cell[:, None, :] + frac) * dx).reshape(-1, 3)
+    n = xyz.shape[0]
+    centre = (np.asarray(cells_lo, np.float64) + 0.5 * np.asarray(cells_n, np.float64)) * dx
+    r = xyz - centre
+    w = np.asarray(omega, np.float64)
+    vel = np.cross(np.broadcast_to(w, r.shape), r)
+    # covariance Q diag(s^2) Q^T, s ~ U(0.1, 0.5) dx, Q a random rotation (from a random unit quaternion)
+    q = rng.standard_normal((n, 4))
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    a, b, c, d = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    Q = np.stack([
+        np.stack([a * a + b * b - c * c - d * d, 2 * (b * c - a * d), 2 * (b * d + a * c)], 1),
+        np.stack([2 * (b * c + a * d), a * a - b * b + c * c - d * d, 2 * (c * d - a * b)], 1),
+        np.stack([2 * (b * d - a * c), 2 * (c * d + a * b), a * a - b * b - c * c + d * d], 1)], 1)
+    s2 = (rng.uniform(0.1, 0.5, (n, 3)) * dx) ** 2
+    S = np.einsum("nij,nj,nkj->nik", Q, s2, Q)
+    cov = np.stack([S[:, 0, 0], S[:, 0, 1], S[:, 0, 2], S[:, 1, 1], S[:, 1, 2], S[:, 2, 2]], 1)
+    vol = np.full(n, dx ** 3 / ppc)
+    f = lambda x: np.ascontiguousarray(x, dtype=np.float32)
+    return {"xyz": f(xyz), "vel": f(vel), "cov": f(cov), "vol": f(vol)}
+
+
+def workload(name, ppc=8, seed=SEED):
+    n_grid, extent, lo, cn, dt = WORKLOADS[name]
+    cloud = make_cloud(n_grid, extent, lo, cn, ppc=ppc, seed=seed)
+    return cloud, sim_args(n_grid=n_grid, grid_extent=extent, substep_dt=dt), block_ops(n_grid, extent, lo, cn)
+
+
+def sim_args(n_grid=64, grid_extent=2.0, material="jelly", E=2e5, nu=0.3, density=1000.0,
+             gravity=(0.0, 0.0, -9.8), substep_dt=1e-4, frame_dt=1e-2, viscosity=0.05, **kw):
+    """Namespace with the MPMParams fields the solver reads (arguments/__init__.py:46-85)."""
+    ns = types.SimpleNamespace(n_grid=n_grid, grid_extent=grid_extent, material=material, E=E, nu=nu,
+                               density=density, gravity=list(gravity), substep_dt=substep_dt, frame_dt=frame_dt,
+                               viscosity=viscosity, fitting=False, boundary_conditions=[])
+    ns.steps_per_frame = int(frame_dt / substep_dt)
+    for k, v in kw.items():
+        setattr(ns, k, v)
+    return ns
+
+
+def block_ops(n_grid, grid_extent, cells_lo, cells_n):
+    """One always-on fixed_cube slab under the block plus the z-plane collider main.py:276 always adds,
+    placed relative to the block so the grid kernel's op list is exercised."""
+    dx = grid_extent / n_grid
+    z0 = cells_lo[2] * dx
+    bcs = [{"id": 0, "type": "fixed_cube", "center": [grid_extent / 2, grid_extent / 2, z0 - 4 * dx],
+            "size": [grid_extent, grid_extent, 2 * dx], "start_time": 0.0, "num_dt": 10 ** 12}]
+    collider = {"point": (0.0, 0.0, z0 - 1.0 * dx), "normal": (0.0, 0.0, 1.0), "friction": 0.0}
+    return {"boundary_conditions": bcs, "collider": collider}

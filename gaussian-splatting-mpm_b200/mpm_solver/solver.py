@@ -1,0 +1,233 @@
+"""MPM_Simulator (reference: mpm_solver/solver.py:9-177) on the B200 kernels.
+
+Drop-in for `from mpm_solver.solver import *` in the reference's main.py: same constructor, same
+`set_boundary_conditions / add_surface_collider / p2g2p / postprocess`, same `mpm_state` /
+`mpm_model` attribute names, plus a `ti` shim because main.py obtains `ti` through the star import
+and calls `ti.init(arch=ti.cuda)` (main.py:7,28).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import torch
+
+from . import _native
+from .model import *            # noqa: F401,F403  (reference does the same star imports)
+from .model import _Backend
+from .utils import *            # noqa: F401,F403
+from .utils import _stream, material_types
+from .collider import *         # noqa: F401,F403
+from .boundary_conditions import *  # noqa: F401,F403
+
+
+class _TiShim:
+    """Stands in for the `taichi` module name main.py expects.  Only CUDA exists here."""
+    cuda = "cuda"
+    gpu = "cuda"
+    cpu = "cpu"
+    f32 = torch.float32
+    i32 = torch.int32
+
+    @staticmethod
+    def init(arch="cuda", **kwargs):
+        if arch != "cuda":
+            raise RuntimeError("this mpm_solver has no CPU path: ti.init(arch=ti.cuda) only")
+        if not torch.cuda.is_available():
+            raise RuntimeError("no CUDA device visible")
+        _native.lib()  # fail loudly now if the extension was not built
+
+
+ti = _TiShim()
+
+
+class MPM_Simulator:
+    def __init__(self, xyzs, covs, volumes, args, init_v=None, strict_q1=True, strict_q3=True, track_cov=False):
+        if getattr(args, "fitting", False):
+            raise NotImplementedError("differentiable path (MPM_state_opt) out of scope")
+        self.n_particles = xyzs.shape[0]
+        device = xyzs.device if xyzs.is_cuda else torch.device("cuda", torch.cuda.current_device())
+        self._backend = _Backend(self.n_particles, args.n_grid, args.grid_extent, device)
+        self.mpm_model = MPM_model(self.n_particles, args, _backend=self._backend)
+        self.mpm_state = MPM_state(self.n_particles, xyzs, covs, volumes, args, _backend=self._backend)
+
+        self.time = 0.0
+
+        self.collider_params = []
+
+        self.particle_preprocess = []
+        self.grid_postprocess = []
+        self.init_particles = []
+
+        self._strict_q1 = strict_q1
+        self._strict_q3 = strict_q3
+        self._track_cov = track_cov
+        self._sync_flags()
+        self._backend.recompute_keys()
+
+    # -- flags / parameters ------------------------------------------------------------------
+    def _has_plastic(self):
+        mat = self._backend.cur["meta"][: self.n_particles, 1]
+        return bool((mat != 0).any().item()) if self.n_particles else False
+
+    def _sync_flags(self):
+        f = 0
+        if self._strict_q1:
+            f |= _native.STRICT_Q1
+        if self._strict_q3:
+            f |= _native.STRICT_Q3
+        if self._track_cov:
+            f |= _native.TRACK_COV
+        if self._has_plastic():
+            f |= _native.WRITE_FTRIAL  # F_trial != F after a return mapping; export needs F_trial
+        self._backend.params.flags = f
+        self.mpm_model._push()
+
+    def set_parameters(self, params=None, **kw):
+        """Update solver parameters from a dict (not in the reference; north_star asks for it).
+        Keys: gravity, E, nu, yield_stress, hardening, xi, plastic_viscosity, softening, friction_angle,
+        strict_q1, strict_q3, track_cov."""
+        p = dict(params or {})
+        p.update(kw)
+        m = self.mpm_model
+        for k, v in p.items():
+            if k == "gravity":
+                m.gravity = tuple(float(g) for g in v)
+            elif k in ("hardening", "xi", "plastic_viscosity", "softening"):
+                setattr(m, k, v)
+            elif k == "friction_angle":
+                m.friction_angle = float(v)
+                sin_phi = math.sin(m.friction_angle / 180.0 * 3.141592653589793)
+                m.alpha = math.sqrt(2.0 / 3.0) * 2.0 * sin_phi / (3.0 - sin_phi)
+            elif k == "yield_stress":
+                m.yield_stress.fill(float(v))
+            elif k == "E":
+                m._logE.fill_(math.log10(v))
+            elif k == "nu":
+                m._y.fill_(-math.log(0.49 / v - 1))
+            elif k in ("strict_q1", "strict_q3", "track_cov"):
+                setattr(self, "_" + k, bool(v))
+            else:
+                raise KeyError(k)
+        if "E" in p or "nu" in p:
+            m.recompute_mu_lam()
+        self._sync_flags()
+
+    set_parameters_dict = set_parameters
+
+    # -- the substep -------------------------------------------------------------------------
+    def _ops_at(self, time) -> _native.SubstepOps:
+        """active impulses and grid operations at `time`, in registration order (solver.py:31-46)"""
+        ops = _native.SubstepOps()
+        ni = 0
+        for pp in self.particle_preprocess:
+            if pp.isActive(time):
+                if ni >= _native.MAX_IMPULSES:
+                    raise _native.MpmkError("too many simultaneous impulses")
+                ops.impulses[ni] = pp.as_impulse()
+                ni += 1
+        ops.n_impulses = ni
+        no = 0
+        for gp in self.grid_postprocess:
+            if gp.isCollide or gp.isActive(time):
+                if no >= _native.MAX_GRID_OPS:
+                    raise _native.MpmkError("too many simultaneous grid operations")
+                ops.ops[no] = gp.as_grid_op()
+                no += 1
+        ops.n_ops = no
+        return ops
+
+    def p2g2p(self, dt):
+        b = self._backend
+        ops = self._ops_at(self.time)
+        b.ctx.call("mpmk_substep", float(dt), C.byref(ops), _stream())
+        b._ftrial_valid = bool(b.params.flags & _native.WRITE_FTRIAL)
+        b.invalidate()
+        self.time += dt
+
+    def step(self, n_substeps, dt=None):
+        """`n_substeps` calls of p2g2p(dt); stretches over which the active BC set is constant are
+        replayed from a CUDA graph (mpmk_substeps).  `time` advances by the same double accumulation
+        as the reference's loop (solver.py:52), so activity windows switch on the same substeps."""
+        b = self._backend
+        dt = float(self.mpm_model.args.substep_dt if dt is None else dt)
+        i = 0
+        while i < n_substeps:
+            ops = self._ops_at(self.time)
+            raw = bytes(ops)
+            t = self.time
+            j = i
+            while j < n_substeps and bytes(self._ops_at(t)) == raw:
+                t += dt
+                j += 1
+            b.ctx.call("mpmk_substeps", dt, C.byref(ops), j - i, _stream())
+            self.time = t
+            i = j
+        b._ftrial_valid = bool(b.params.flags & _native.WRITE_FTRIAL)
+        b.invalidate()
+
+    # -- registries: solver.py:110-129, :140-166 ---------------------------------------------
+    def set_boundary_conditions(self, bc_args_arr, sim_args):
+        for bc_args in bc_args_arr:
+            bc_type = bc_args["type"]
+
+            bc = boundaryConditionTypeCallBacks[bc_type](self.n_particles, bc_args, sim_args)
+
+            if bc.type in preprocess_bc:
+                self.particle_preprocess.append(bc)
+
+            if bc.type in postprocess_bc:
+                self.grid_postprocess.append(bc)
+
+            if bc.type in init_bc:
+                self.init_particles.append(bc)
+
+        for pp in self.init_particles:
+            pp.apply(self.mpm_state, self.mpm_model)
+            if pp.isMaterial == False:
+                self.mpm_model.recompute_mu_lam()
+                pp.applymu(self.mpm_state, self.mpm_model)
+        self._sync_flags()
+
+    def add_surface_collider(
+        self,
+        point,
+        normal,
+        surface="sticky",  # accepted and ignored, as in the reference (solver.py:144)
+        friction=0.0,
+        start_time=0.0,    # ignored (solver.py:146)
+        end_time=999.0,    # ignored (solver.py:147)
+    ):
+        point = list(point)
+        normal_scale = 1.0 / math.sqrt(float(sum(x ** 2 for x in normal)))
+        normal = list(normal_scale * x for x in normal)
+        collider_param = MPM_Collider(point, normal, friction)
+        self.collider_params.append(collider_param)
+        cl = collideTypeCallBacks["ground"](collider_param.point, collider_param.normal, collider_param.friction)
+        self.grid_postprocess.append(cl)
+
+    def postprocess(self):
+        """solver.py:135-137: compute_cov_from_F + compute_R_from_F, fused with the scatter to
+        original particle order into persistent torch buffers (csrc/export.cu)."""
+        b = self._backend
+        b.export(want_R=True)
+        b.cov_from_postprocess = True
+
+    def export(self):
+        """(xyz [N,3], cov [N,6], R [N,3,3]) CUDA tensors in original particle order, no host copy."""
+        b = self._backend
+        if not b.export_fresh:
+            self.postprocess()
+        return b.out_xyz, b.out_cov, b.out_R
+
+    def counters(self):
+        c = _native.Counters()
+        self._backend.ctx.call("mpmk_read_counters", C.byref(c), _stream())
+        return {k: getattr(c, k) for k, _ in c._fields_}
+
+    # -- differentiable API of the reference (solver.py:54-108,131-133,168-177): out of scope --
+    def _no_grad(self, *a, **k):
+        raise NotImplementedError("differentiable path out of scope")
+
+    p2g2p_forward = p2g2p_backward = learn = set_bc_ground_only = _no_grad
+    postprocess_forward = postprocess_backward = clear_grads = _no_grad

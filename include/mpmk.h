@@ -1,0 +1,197 @@
+/*
+ * mpmk.h -- C ABI of libmpmk.so: the B200 (sm_100a) MPM substep kernels.
+ *
+ * This is the drop-in boundary for the hot path `MPM_Simulator.p2g2p()` of
+ * ranrandy/gaussian-splatting-mpm (mpm_solver/solver.py:27-52).  The reference
+ * has no FFI of its own: its kernels are Taichi `@ti.kernel`s JIT-compiled by
+ * taichi==1.5.0.  Each entry point below therefore names the reference kernel
+ * (file:line, relative to the reference root) whose work it replaces.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every `dev` pointer is a CUDA device
+ *     pointer owned by the caller (torch tensors in the Python host layer);
+ *     the library borrows them and owns only its scratch (sort buffers,
+ *     histograms, work lists).
+ *   - every launch goes to the caller's stream (`stream` = cudaStream_t cast to
+ *     void*); no entry point synchronises unless its comment says so.
+ *   - return value 0 = success, otherwise a cudaError_t-compatible code (or
+ *     MPMK_ERR_*); the message is available from mpmk_last_error().
+ *   - a context is bound to one device and is not thread-safe.
+ */
+#ifndef MPMK_H
+#define MPMK_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MPMK_VERSION 1
+
+#if defined(__GNUC__)
+#define MPMK_API __attribute__((visibility("default")))
+#else
+#define MPMK_API
+#endif
+
+#define MPMK_ERR_INVALID 10001 /* bad argument                      */
+#define MPMK_ERR_STATE 10002   /* call order / missing bind         */
+
+/* material ids: mpm_solver/utils.py:5-10 (0..3); 4 and 5 are additions of
+ * this build, parity unpinned                               */
+#define MPMK_MAT_JELLY 0
+#define MPMK_MAT_METAL 1
+#define MPMK_MAT_SAND 2
+#define MPMK_MAT_FOAM 3
+#define MPMK_MAT_FLUID 4
+#define MPMK_MAT_PLASTICINE 5
+
+/* behaviour flags (mpmk_params.flags) */
+#define MPMK_STRICT_Q1 1u  /* utils.py:37: jelly stress is never evaluated -> 0       */
+#define MPMK_STRICT_Q3 2u  /* constitutive_models.py:256: foam F through Hadamard     */
+#define MPMK_WRITE_FTRIAL 4u /* g2p also stores F_trial (needed by export for plastic)  */
+#define MPMK_TRACK_COV 8u  /* g2p applies update_cov every substep (utils.py:187-215) */
+
+typedef struct mpmk_ctx mpmk_ctx;
+
+/* One set of particle arrays in the packed SoA the kernels use; each array
+ * holds `capacity` 16-byte records, record r belongs to the particle in
+ * physical slot r.  Two sets are bound (ping-pong): g2p reads the source set
+ * through the sort permutation and writes the destination set in sorted
+ * order, which re-establishes physical order == sorted order every substep.  */
+typedef struct {
+    void* xm;   /* float4 {x, y, z, mass}              model.py:85,87           */
+    void* vv;   /* float4 {vx, vy, vz, -}              model.py:88              */
+    void* c0;   /* float4 {C00, C01, C02, C10}         model.py:91              */
+    void* c1;   /* float4 {C11, C12, C20, C21}                                  */
+    void* cs;   /* float4 {C22, s00, s01, s02}         stress: model.py:90      */
+    void* s1;   /* float4 {s11, s12, s22, vol}         symmetric Kirchhoff stress */
+    void* f0;   /* float4 {F00, F01, F02, F10}         model.py:89              */
+    void* f1;   /* float4 {F11, F12, F20, F21}                                  */
+    void* f2;   /* float4 {F22, mu, lam, yield_stress} model.py:38-39,54        */
+    void* meta; /* int4   {orig_id, material, vol(bits), 0}                     */
+    void* cv0;  /* float4 {cov0..cov3}  only read/written with MPMK_TRACK_COV   */
+    void* cv1;  /* float4 {cov4, cov5, -, -}                                    */
+} mpmk_particle_set;
+
+typedef struct {
+    mpmk_particle_set set[2];
+    void* ft0;      /* float4 x3: F_trial of the last g2p, sorted order (model.py:98) */
+    void* ft1;
+    void* ft2;
+    void* keys;     /* uint32[capacity]: cell key of the particle in each physical slot */
+    void* grid_in;  /* float4[n^3] {px, py, pz, mass}  grid_v_in + grid_mass, model.py:118-120 */
+    void* grid_out; /* float4[n^3] {vx, vy, vz, 0}     grid_v_out, model.py:121        */
+} mpmk_bindings;
+
+typedef struct {
+    float gravity[3];        /* model.py:32                                   */
+    float alpha;             /* model.py:49-51                                */
+    float plastic_viscosity; /* model.py:58                                   */
+    float xi;                /* model.py:57                                   */
+    float softening;         /* model.py:59                                   */
+    int32_t hardening;       /* model.py:56                                   */
+    uint32_t flags;          /* MPMK_STRICT_* | MPMK_WRITE_FTRIAL | MPMK_TRACK_COV */
+} mpmk_params;
+
+/* grid operations applied after normalisation, in list order (solver.py:41-46) */
+#define MPMK_OP_FIXED_CUBE 0 /* boundary_conditions.py:23-27: a=center, b=size          */
+#define MPMK_OP_COLLIDER 1   /* collider.py:13-44: a=point, b=unit normal, c=friction   */
+typedef struct {
+    int32_t type;
+    float a[3];
+    float b[3];
+    float c;
+} mpmk_grid_op;
+
+/* particle pre-process: boundary_conditions.py:41-45 ImpulseBC.apply */
+typedef struct {
+    float center[3];
+    float size[3];
+    float force[3];
+    float substep_dt; /* the BC's own substep_dt, not the call's dt */
+} mpmk_impulse;
+
+#define MPMK_MAX_GRID_OPS 16
+#define MPMK_MAX_IMPULSES 8
+
+typedef struct {
+    int32_t n_ops;
+    mpmk_grid_op ops[MPMK_MAX_GRID_OPS];
+    int32_t n_impulses;
+    mpmk_impulse impulses[MPMK_MAX_IMPULSES];
+} mpmk_substep_ops;
+
+/* device-side counters of the last substep (mpmk_read_counters copies them) */
+typedef struct {
+    uint32_t n_items;         /* p2g work items (tile chunks)                  */
+    uint32_t n_active_blocks; /* 4x4x4-node blocks touched by p2g              */
+    uint32_t n_tiles;         /* non-empty 4x4x4-cell tiles                    */
+    uint32_t n_clamped;       /* particles whose base cell was clamped (Q9)    */
+} mpmk_counters;
+
+/* ---- lifecycle ---------------------------------------------------------- */
+MPMK_API int mpmk_version(void);
+/* dx = grid_extent/n_grid and inv_dx = n_grid/grid_extent are computed in double
+ * and rounded to f32 as model.py:15-16 does.  Allocates the scratch.          */
+MPMK_API int mpmk_create(mpmk_ctx** out, int device, int n_grid, double grid_extent, int64_t capacity);
+MPMK_API int mpmk_destroy(mpmk_ctx* ctx);
+MPMK_API const char* mpmk_last_error(mpmk_ctx* ctx);
+MPMK_API int mpmk_bind(mpmk_ctx* ctx, const mpmk_bindings* b);
+MPMK_API int mpmk_set_params(mpmk_ctx* ctx, const mpmk_params* p);
+/* number of live particles and which set currently holds them (0 or 1) */
+MPMK_API int mpmk_set_count(mpmk_ctx* ctx, int64_t n_particles, int current_set);
+MPMK_API int mpmk_current_set(mpmk_ctx* ctx);
+MPMK_API int64_t mpmk_count(mpmk_ctx* ctx);
+
+/* ---- init-time kernels --------------------------------------------------- */
+/* utils.py:350-362 compute_mu_lam_from_E_nu */
+MPMK_API int mpmk_compute_mu_lam(mpmk_ctx* ctx, int64_t n, const void* logE_dev, const void* y_dev, void* mu_dev,
+                        void* lam_dev, void* stream);
+/* internel_filling/filling.py:12-24; cell_count_dev = int32[n_grid^3] scratch, zeroed by the caller */
+MPMK_API int mpmk_particle_volume(mpmk_ctx* ctx, int64_t n, const void* pos_dev /* float[n][3] */, float grid_dx,
+                         void* cell_count_dev, void* vol_dev, void* stream);
+/* cell keys of the current set from positions (utils.py:94-95 base cell) */
+MPMK_API int mpmk_compute_keys(mpmk_ctx* ctx, void* stream);
+/* utils.py:14-54 compute_stress_from_F_trial on the current set, in place:
+ * F <- return_map(F), stress <- tau(F).  Used after init / from_torch edits. */
+MPMK_API int mpmk_constitutive(mpmk_ctx* ctx, float dt, void* stream);
+
+/* ---- the substep, stage by stage (solver.py:27-52) ------------------------ */
+/* stable LSD radix sort of (key, slot) by key; results stay in library scratch */
+MPMK_API int mpmk_sort(mpmk_ctx* ctx, void* stream);
+/* copy the last sort's sorted keys / permutation (uint32[n]) to caller buffers */
+MPMK_API int mpmk_get_sort_result(mpmk_ctx* ctx, void* sorted_keys_dev, void* perm_dev, void* stream);
+/* model.py:124-127 reset_grid_state, restricted to the blocks the previous
+ * substep touched; then tile work list + active-block list of this substep   */
+MPMK_API int mpmk_prepare_grid(mpmk_ctx* ctx, void* stream);
+/* boundary_conditions.py:41-45 (impulses) + utils.py:90-134 p2g */
+MPMK_API int mpmk_p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, void* stream);
+/* utils.py:178-183 + boundary_conditions.py:23-27 + collider.py:13-44, fused */
+MPMK_API int mpmk_grid_update(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, void* stream);
+/* utils.py:219-282 g2p + :14-54 compute_stress_from_F_trial (for the next
+ * substep) + new cell keys; writes the other set in sorted order and flips   */
+MPMK_API int mpmk_g2p(mpmk_ctx* ctx, float dt, void* stream);
+/* all of the above in order: one reference p2g2p() call */
+MPMK_API int mpmk_substep(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, void* stream);
+/* n substeps with constant dt and ops, replayed from a CUDA graph */
+MPMK_API int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, int n, void* stream);
+
+/* ---- export (solver.py:135-137 postprocess + main.py:311-312) ------------- */
+/* utils.py:402-433 compute_cov_from_F and :377-398 compute_R_from_F fused with
+ * the scatter back to original particle order.  Any output may be NULL.
+ * init_cov_dev: float[n][6] in ORIGINAL order.                                */
+MPMK_API int mpmk_export(mpmk_ctx* ctx, const void* init_cov_dev, void* xyz_out_dev /* float[n][3] */,
+                void* cov_out_dev /* float[n][6] */, void* R_out_dev /* float[n][9] */, void* stream);
+
+/* ---- introspection -------------------------------------------------------- */
+/* synchronises `stream` */
+MPMK_API int mpmk_read_counters(mpmk_ctx* ctx, mpmk_counters* out, void* stream);
+/* how many kernels the library has launched since create (for bench's gpu_launches) */
+MPMK_API int64_t mpmk_launch_count(mpmk_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MPMK_H */
