@@ -48,6 +48,8 @@ static int create_impl(mpmk_ctx* ctx, int device, int n_grid, double grid_extent
     ALLOC0(ctx, ctx->block_count[1], 4);
     ALLOC0(ctx, ctx->counters, sizeof(DevCounters));
     ALLOC0(ctx, ctx->dev_stamp, 4);
+    MPMK_CHECK(ctx, cudaStreamCreateWithFlags(&ctx->cap_stream, cudaStreamNonBlocking));
+    { int rc = mpmk_p2g_init(ctx); if (rc) return rc; }
     ctx->prm.alpha = 0.0f;
     return 0;
 }
@@ -67,6 +69,7 @@ extern "C" int mpmk_destroy(mpmk_ctx* ctx) {
     cudaFree(ctx->hist); cudaFree(ctx->hist_tot); cudaFree(ctx->items); cudaFree(ctx->block_stamp);
     cudaFree(ctx->block_list[0]); cudaFree(ctx->block_list[1]); cudaFree(ctx->block_count[0]); cudaFree(ctx->block_count[1]);
     cudaFree(ctx->counters); cudaFree(ctx->dev_stamp);
+    if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
     delete ctx;
     return 0;
 }
@@ -198,16 +201,17 @@ extern "C" int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* op
     e.n_steps = n_steps; e.dt = dt; e.cur = ctx->cur; e.cur_list = ctx->cur_list; e.flags = user_flags; e.n = ctx->n;
     e.ops = *ops; e.b = ctx->b;
     const int64_t launches_before = ctx->launches;
-    MPMK_CHECK(ctx, cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+    cudaStream_t cs = ctx->cap_stream;
+    MPMK_CHECK(ctx, cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
     int rc = 0;
     for (int i = 0; i < n_steps && rc == 0; ++i) {
         // F_trial is only consumed by export: store it on the last substep of the batch only
         ctx->prm.flags = (i == n_steps - 1) ? user_flags : (user_flags & ~MPMK_WRITE_FTRIAL);
-        rc = substep_impl(ctx, dt, ops, s);
+        rc = substep_impl(ctx, dt, ops, cs);
     }
     ctx->prm.flags = user_flags;
     cudaGraph_t graph = nullptr;
-    cudaError_t ce = cudaStreamEndCapture(s, &graph);
+    cudaError_t ce = cudaStreamEndCapture(cs, &graph);
     if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
     MPMK_CHECK(ctx, ce);
     cudaGraphExec_t exec = nullptr;

@@ -72,6 +72,7 @@ struct mpmk_ctx {
         mpmk_bindings b;
     } graphs[4];
     int n_graphs;
+    cudaStream_t cap_stream;  // graphs are captured here (the legacy default stream cannot be captured)
     char err[512];
 };
 
@@ -131,3 +132,4 @@ int mpmk_launch_prepare(mpmk_ctx* ctx, cudaStream_t s);
 int mpmk_launch_p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);
 int mpmk_launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);
 int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s);
+int mpmk_p2g_init(mpmk_ctx* ctx);

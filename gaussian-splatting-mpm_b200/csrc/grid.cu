@@ -29,17 +29,21 @@ __global__ void __launch_bounds__(256) k_grid(const float4* __restrict__ gin, fl
             vy = __fdiv_rn(m.y, m.w) + dt * gy;
             vz = __fdiv_rn(m.z, m.w) + dt * gz;
         }
-        float px = (float)ix * dx, py = (float)iy * dx, pz = (float)iz * dx;
+        // geometric predicates are discontinuous: keep every product and difference individually rounded
+        // (no FMA contraction) so a node lying exactly on a box face / collider plane falls on the same
+        // side as in the reference arithmetic (float(idx) * dx - c)
+        const float px = __fmul_rn((float)ix, dx), py = __fmul_rn((float)iy, dx), pz = __fmul_rn((float)iz, dx);
         for (int o = 0; o < ops.n_ops; ++o) {
             const mpmk_grid_op& op = ops.ops[o];
             if (op.type == MPMK_OP_FIXED_CUBE) {
-                if (fabsf(px - op.a[0]) < op.b[0] && fabsf(py - op.a[1]) < op.b[1] && fabsf(pz - op.a[2]) < op.b[2]) {
+                if (fabsf(__fsub_rn(px, op.a[0])) < op.b[0] && fabsf(__fsub_rn(py, op.a[1])) < op.b[1] &&
+                    fabsf(__fsub_rn(pz, op.a[2])) < op.b[2]) {
                     vx = 0.f; vy = 0.f; vz = 0.f;
                 }
             } else {
-                float ox = px - op.a[0], oy = py - op.a[1], oz = pz - op.a[2];
-                float nx = op.b[0], ny = op.b[1], nz = op.b[2];
-                float dp = ox * nx + oy * ny + oz * nz;
+                const float ox = __fsub_rn(px, op.a[0]), oy = __fsub_rn(py, op.a[1]), oz = __fsub_rn(pz, op.a[2]);
+                const float nx = op.b[0], ny = op.b[1], nz = op.b[2];
+                const float dp = __fadd_rn(__fadd_rn(__fmul_rn(ox, nx), __fmul_rn(oy, ny)), __fmul_rn(oz, nz));
                 if (dp < 0.f) {
                     float nc = vx * nx + vy * ny + vz * nz;
                     float mn = fminf(nc, 0.f);

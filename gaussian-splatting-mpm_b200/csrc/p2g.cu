@@ -214,16 +214,16 @@ int mpmk_launch_p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaSt
         a.n_imp = ops->n_impulses;
         memcpy(a.imp, ops->impulses, sizeof(mpmk_impulse) * ops->n_impulses);
     }
-    static bool attr_set = false;
     const int smem = (int)sizeof(P2GWarpSmem) * P2G_WARPS;
-    if (!attr_set) {
-        MPMK_CHECK(ctx, cudaFuncSetAttribute(k_p2g, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr_set = true;
-    }
     // persistent grid: 2 CTAs per SM, warps fetch items dynamically
     int64_t want = (ctx->n / 32 + P2G_WARPS - 1) / P2G_WARPS + 1;
     int grid = (int)(want < (int64_t)ctx->sm_count * 2 ? want : (int64_t)ctx->sm_count * 2);
     k_p2g<<<grid, P2G_WARPS * 32, smem, s>>>(a);
     MPMK_LAUNCH_CHECK(ctx);
+    return 0;
+}
+
+int mpmk_p2g_init(mpmk_ctx* ctx) {
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_p2g, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(P2GWarpSmem) * P2G_WARPS));
     return 0;
 }
