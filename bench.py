@@ -1,0 +1,309 @@
+#!/usr/bin/env python
+"""bench.py -- MPM particle-substeps/s (sort + P2G + grid + G2P) on synthetic particle clouds.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+
+One "step" = one frame-sized batch of SUBSTEPS_PER_STEP substeps (reference: the inner loop of
+main.py:305-306) over one synthetic cloud.  N=1 runs the S-4M cloud (4,096,000 particles, 256^3
+grid), the configuration BASELINE.json's metric is quoted on; N>1 runs the slab-decomposed bar
+(S-32M-bar scaled to N ranks, weak scaling).  Rank 0 prints ONE JSON line.
+
+--impl reference times the reference's own algorithm on the host cores: Taichi is not installable
+here, so this is oracle/mpm_oracle.c's OpenMP build, the CPU restatement of the
+reference kernels (no sort, dense grid passes), on the same cloud.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "gaussian-splatting-mpm_b200")
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+SUBSTEPS_PER_STEP = 10
+METRIC = "particle_substeps_per_sec"
+UNIT = "particle-substeps/s"
+
+
+def _peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        for t, line in self.rows:
+            if t < t0 - 0.05 or t > t1 + 0.15:
+                continue
+            parts = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(parts[0])); mx = float(parts[1])
+            except Exception:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def _cpu_reference(cloud, args, ops, substeps, warm=1):
+    """the reference algorithm (no sort, dense grid passes) on all host cores; returns (pss, secs, cores)"""
+    from oracle import mpm_oracle as O
+    cores = len(os.sched_getaffinity(0))
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    sim = O.OracleSim(cloud["xyz"], cloud["cov"], cloud["vol"], args, omp=True, sort=False, strict_q1=False, track_cov=True)
+    sim.particle_vel[:] = cloud["vel"]
+    sim.set_boundary_conditions(ops["boundary_conditions"], args)
+    c = ops["collider"]
+    sim.add_surface_collider(c["point"], c["normal"], friction=c["friction"])
+    for _ in range(warm):
+        sim.p2g2p(args.substep_dt)
+    t0 = time.time()
+    for _ in range(substeps):
+        sim.p2g2p(args.substep_dt)
+    dt = time.time() - t0
+    return sim.n_particles * substeps / dt, dt, sim.L.orc_num_threads()
+
+
+def run_reference(a, rank, world):
+    if rank != 0:
+        return
+    from harness import synthetic
+    name = a.workload or "S-4M"
+    cloud, args, ops = synthetic.workload(name)
+    n = cloud["xyz"].shape[0]
+    times = []
+    from oracle import mpm_oracle as O
+    cores = len(os.sched_getaffinity(0))
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    sim = O.OracleSim(cloud["xyz"], cloud["cov"], cloud["vol"], args, omp=True, sort=False, strict_q1=False, track_cov=True)
+    sim.particle_vel[:] = cloud["vel"]
+    sim.set_boundary_conditions(ops["boundary_conditions"], args)
+    c = ops["collider"]
+    sim.add_surface_collider(c["point"], c["normal"], friction=c["friction"])
+    sub = 1  # bounded sample: one substep of the full cloud per step
+    for i in range(a.warmup + a.steps):
+        t0 = time.time()
+        for _ in range(sub):
+            sim.p2g2p(args.substep_dt)
+        if i >= a.warmup:
+            times.append(time.time() - t0)
+    total = sum(times)
+    value = n * sub * a.steps / total
+    sample = f"full {name} cloud ({n} particles, {args.n_grid}^3 dense grid), {sub} substep per step"
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": 1e3 * total / a.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": name, "particles": n, "n_grid": args.n_grid, "material": "jelly (FCR)",
+                       "substeps_per_step": sub, "note": "CPU restatement of the reference's Taichi kernels (oracle/mpm_oracle.c, "
+                       "OpenMP, omp-atomic P2G); Taichi itself is not installable here"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": sim.L.orc_num_threads(), "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=None)
+    ap.add_argument("--material", default="jelly")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--substeps", type=int, default=SUBSTEPS_PER_STEP)
+    a = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if a.impl == "reference":
+        run_reference(a, rank, world)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from harness import synthetic
+    if a.warmup < 3:
+        a.warmup = 3
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from mpm_solver.solver import MPM_Simulator
+    from mpm_solver import _native
+
+    if world > 1:
+        from harness import slabs
+        slabs.bench_multi(a, rank, world, dev)
+        return
+
+    name = a.workload or "S-4M"
+    cloud, args, ops = synthetic.workload(name)
+    args.material = a.material
+    n = cloud["xyz"].shape[0]
+    S = a.substeps
+    dt = args.substep_dt
+    pin = {k: torch.from_numpy(v).pin_memory() for k, v in cloud.items()}
+    sim = MPM_Simulator(pin["xyz"].to(dev), pin["cov"].to(dev), pin["vol"].to(dev), args, strict_q1=False)
+    sim.set_boundary_conditions(ops["boundary_conditions"], args)
+    sim.add_surface_collider(ops["collider"]["point"], ops["collider"]["normal"], friction=ops["collider"]["friction"])
+    sim.mpm_state.particle_vel.from_torch(pin["vel"].to(dev))
+    L, h = sim._backend.ctx.L, sim._backend.ctx.h
+    stream = torch.cuda.current_stream()
+
+    def barrier():
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput: K steps of S graph-replayed substeps, inputs already in HBM ----
+    for _ in range(a.warmup):
+        sim.step(S, dt)
+    barrier()
+    l0 = L.mpmk_launch_count(h)
+    sim.p2g2p(dt)                      # one eager substep to count kernels per substep
+    kernels_per_substep = L.mpmk_launch_count(h) - l0
+    barrier()
+    sampler = ClockSampler(local)
+    time.sleep(0.3)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.time()
+    ev0.record(stream)
+    for _ in range(a.steps):
+        sim.step(S, dt)
+    ev1.record(stream)
+    barrier()
+    t1 = time.time()
+    ms = ev0.elapsed_time(ev1)
+    clocks = sampler.stop(t0, t1)
+    value = n * S * a.steps / (ms * 1e-3)
+
+    # ---- per-stage durations (CUDA events around each stage on the launching stream) ----
+    b = sim._backend
+    import ctypes as C
+    sops = sim._ops_at(sim.time)
+    stages = ["sort", "prepare", "p2g", "grid", "g2p"]
+    acc = {k: 0.0 for k in stages}
+    reps = max(10, S)
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(6)] for _ in range(reps)]
+    sp = stream.cuda_stream
+    for r in range(reps):
+        e = evs[r]
+        e[0].record(stream); b.ctx.call("mpmk_sort", sp)
+        e[1].record(stream); b.ctx.call("mpmk_prepare_grid", sp)
+        e[2].record(stream); b.ctx.call("mpmk_p2g", dt, C.byref(sops), sp)
+        e[3].record(stream); b.ctx.call("mpmk_grid_update", dt, C.byref(sops), sp)
+        e[4].record(stream); b.ctx.call("mpmk_g2p", dt, sp)
+        e[5].record(stream)
+    barrier()
+    for r in range(reps):
+        for i, k in enumerate(stages):
+            acc[k] += evs[r][i].elapsed_time(evs[r][i + 1]) / reps
+    touched = int((b.grid_in[..., 3] > 0).sum().item())
+    peak, peak_src = _peaks()
+    alg = {"p2g": 68.0 * n + 16.0 * touched, "g2p": 148.0 * n + 12.0 * touched, "grid": 28.0 * touched,
+           "prepare": 16.0 * touched, "sort": 0.0}
+    dom = max(("p2g", "g2p"), key=lambda k: acc[k])
+    achieved = alg[dom] / (acc[dom] * 1e-3) / 1e9
+    sub_bytes = 216.0 * n + 72.0 * touched
+    fused_ms = acc["p2g"] + acc["grid"] + acc["g2p"]
+    allin_ms = ms / (a.steps * S)
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get(dom)
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "kernel": "k_" + dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg[dom],
+                "kernel_ms": acc[dom], "stage_ms": acc,
+                "substep": {"algorithmic_bytes": sub_bytes, "touched_nodes": touched,
+                            "fused_p2g_grid_g2p_ms": fused_ms, "fused_frac": sub_bytes / (fused_ms * 1e-3) / 1e9 / peak,
+                            "all_in_ms": allin_ms, "all_in_frac": sub_bytes / (allin_ms * 1e-3) / 1e9 / peak}}
+
+    # ---- end to end through the public API with HOST buffers: upload, S substeps, postprocess, download ----
+    out_xyz = torch.empty((n, 3), dtype=torch.float32).pin_memory()
+    out_cov = torch.empty((n, 6), dtype=torch.float32).pin_memory()
+    h2d = n * (3 + 6 + 1 + 3) * 4
+    d2h = n * (3 + 6) * 4
+
+    def e2e_step():
+        sim.load_particles(pin["xyz"].to(dev, non_blocking=True), pin["cov"].to(dev, non_blocking=True),
+                           pin["vol"].to(dev, non_blocking=True))
+        sim.mpm_state.particle_vel.from_torch(pin["vel"].to(dev, non_blocking=True))
+        sim.step(S, dt)
+        sim.postprocess()
+        out_xyz.copy_(sim.mpm_state.particle_xyz.to_torch(), non_blocking=True)
+        out_cov.copy_(sim.mpm_state.particle_cov.to_torch().view(n, 6), non_blocking=True)
+
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ke = max(3, min(a.steps, 5))
+    e0.record(stream)
+    for _ in range(ke):
+        e2e_step()
+    e1.record(stream)
+    barrier()
+    e2e_ms = e0.elapsed_time(e1)
+    e2e = {"value": n * S * ke / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+           "ms_per_step": e2e_ms / ke, "steps": ke,
+           "what": "load_particles(host xyz,cov,vol,vel) + step(S) + postprocess() + D2H xyz,cov (main.py:305-313 loop body)"}
+    assert bool(torch.isfinite(out_xyz).all())
+
+    cpu = None
+    if not a.no_cpu_baseline:
+        v, secs, cores = _cpu_reference(cloud, args, ops, substeps=2)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"full {name} cloud ({n} particles, dense {args.n_grid}^3 grid), 2 substeps after 1 warm-up, {secs:.1f} s"}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": name, "particles": n, "n_grid": args.n_grid, "particles_per_cell": 8, "material": a.material +
+                       (" (FCR, intended mode)" if a.material == "jelly" else ""), "substeps_per_step": S, "substep_dt": dt,
+                       "l2": "particle state 160 B x 4.1 M x 2 buffers >> 126 MB L2: inputs larger than L2, no flush needed",
+                       "parallelism": "single GPU"},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+            "gpu_launches": int(kernels_per_substep * S * a.steps), "kernels_per_substep": int(kernels_per_substep),
+            "clocks": clocks}
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -82,6 +82,12 @@ class _Backend:
         """original particle id of each physical slot (int64[n])"""
         return self.cur["meta"][: self.n, 0].long()
 
+    def reset_order(self):
+        """physical order := original order, in set 0"""
+        self.ctx.call("mpmk_set_count", self.n, 0)
+        self.sets[0]["meta"][: self.n, 0] = torch.arange(self.n, dtype=torch.int32, device=self.device)
+        self.sets[0]["meta"][: self.n, 3] = 0
+
     def invalidate(self):
         self.export_fresh = False
         self.cov_from_postprocess = False
@@ -345,10 +351,9 @@ class MPM_model:
             raise TypeError("Material not supported yet")
         self.gravity = tuple(float(g) for g in self.args.gravity)
         self.material = _MaterialField(b, [("meta", 1)], (), dtype=torch.int32, after_write=b.invalidate)
-        n = b.n
-        for s in b.sets:
-            s["meta"][:n, 0] = torch.arange(n, dtype=torch.int32, device=b.device)
-            s["meta"][:n, 1] = args_material
+        self._args_material = args_material
+        b.reset_order()
+        b.sets[0]["meta"][: b.n, 1] = args_material
 
     def init_elasiticity_params(self):  # model.py:35-46
         b = self._backend
@@ -388,6 +393,16 @@ class MPM_model:
         self.xi = 1
         self.plastic_viscosity = 0.008
         self.softening = 1.0
+
+    def _reinit_packed(self):
+        """refill the per-particle model parameters that live in the packed arrays (material, mu, lam,
+        yield_stress) from the constructor arguments -- used when the particle set is reloaded."""
+        b = self._backend
+        b.cur["meta"][: b.n, 1] = self._args_material
+        self._logE.fill_(math.log10(self.args.E))
+        self._y.fill_(-math.log(0.49 / self.args.nu - 1))
+        self.recompute_mu_lam()
+        self.yield_stress.fill(0.005)
 
     def _push(self):
         """send the scalar model parameters to the library"""
@@ -437,24 +452,40 @@ class MPM_state:
         self.particle_F_trial = _FTrialField(b, F)
 
         # initialisation, model.py:101-115
-        if n > 0:
-            vol = volumes.to(device=dev, dtype=torch.float32).reshape(n)
-            self.particle_vol.from_torch(vol)
-            mass = torch.empty(n, dtype=torch.float32, device=dev)
-            compute_mass_from_vol_density(n, self.particle_density.t, vol, mass)
-            self.particle_mass.from_torch(mass)
-            self._xyz_packed.from_torch(xyzs.to(device=dev, dtype=torch.float32).reshape(n, 3))
-            self.particle_vel.fill(0.0)
-            self.init_identity_mat(self.particle_F)
-            self.particle_stress.fill(0.0)
-            self.particle_C.fill(0.0)
-            b.init_cov.copy_(covs.to(device=dev, dtype=torch.float32).reshape(n, 6))
-            self._cov_packed.from_torch(b.init_cov)
+        self._args_density = float(args.density)
+        self._init_particles(xyzs, covs, volumes)
 
         # grid, model.py:117-122 -- zero-copy views of the float4 node arrays
         self.grid_mass = _GridField(b.grid_in, 3)
         self.grid_v_in = _GridField(b.grid_in, slice(0, 3))
         self.grid_v_out = _GridField(b.grid_out, slice(0, 3))
+
+    def _init_particles(self, xyzs, covs, volumes):
+        """model.py:101-115 on the packed arrays; physical order == original order afterwards."""
+        b = self._backend
+        n, dev = b.n, b.device
+        if n == 0:
+            return
+        b.reset_order()
+        cur = b.cur
+        vol = volumes.to(device=dev, dtype=torch.float32, non_blocking=True).reshape(n)
+        cur["s1"][:n, 3] = vol
+        cur["meta"][:n, 2] = vol.contiguous().view(torch.int32)
+        compute_mass_from_vol_density(n, self.particle_density.t, vol, cur["xm"][:n, 3])
+        cur["xm"][:n, :3] = xyzs.to(device=dev, dtype=torch.float32, non_blocking=True).reshape(n, 3)
+        cur["vv"][:n].zero_()
+        for a in ("c0", "c1", "cs"):
+            cur[a][:n].zero_()
+        cur["s1"][:n, :3] = 0.0
+        cur["f0"][:n] = torch.tensor([1.0, 0.0, 0.0, 0.0], device=dev)
+        cur["f1"][:n] = torch.tensor([1.0, 0.0, 0.0, 0.0], device=dev)
+        cur["f2"][:n, 0] = 1.0
+        b.init_cov.copy_(covs.to(device=dev, dtype=torch.float32, non_blocking=True).reshape(n, 6))
+        cur["cv0"][:n] = b.init_cov[:, :4]
+        cur["cv1"][:n, :2] = b.init_cov[:, 4:]
+        b._ftrial_valid = False
+        b.invalidate()
+        b.recompute_keys()
 
     def reset_grid_state(self):
         """model.py:124-127.  The substep clears only the blocks it touched; this is the dense version."""

@@ -63,7 +63,21 @@ class MPM_Simulator:
         self._strict_q3 = strict_q3
         self._track_cov = track_cov
         self._sync_flags()
-        self._backend.recompute_keys()
+
+    def load_particles(self, xyzs, covs, volumes):
+        """Re-initialise the simulator in place from new particle data (same N): the constructor's state
+        initialisation (model.py:101-115) without reallocating.  Registered boundary conditions stay."""
+        if xyzs.shape[0] != self.n_particles:
+            raise ValueError("load_particles: particle count must not change")
+        self.mpm_state._init_particles(xyzs, covs, volumes)
+        self.mpm_model._reinit_packed()
+        for pp in self.init_particles:
+            pp.apply(self.mpm_state, self.mpm_model)
+            if pp.isMaterial == False:
+                self.mpm_model.recompute_mu_lam()
+                pp.applymu(self.mpm_state, self.mpm_model)
+        self.time = 0.0
+        self._sync_flags()
 
     # -- flags / parameters ------------------------------------------------------------------
     def _has_plastic(self):
