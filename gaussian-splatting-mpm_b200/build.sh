@@ -4,15 +4,17 @@ set -euo pipefail
 cd "$(dirname "$0")"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -Xcompiler -fvisibility=hidden"
-mkdir -p build lib
+OUT=${OUT:-lib/libmpmk.so}
+BUILD=${BUILD:-build}
+mkdir -p "$BUILD" "$(dirname "$OUT")"
 pids=()
 for f in csrc/*.cu; do
-  o=build/$(basename "${f%.cu}").o
+  o=$BUILD/$(basename "${f%.cu}").o
   if [ ! -f "$o" ] || [ "$f" -nt "$o" ] || [ -n "$(find csrc ../include -name '*.cuh' -newer "$o" -o -name '*.h' -newer "$o")" ]; then
-    $NVCC $FLAGS ${PTXAS_V:+-Xptxas -v} -c "$f" -o "$o" &
+    $NVCC $FLAGS ${EXTRA_DEFS:-} ${PTXAS_V:+-Xptxas -v} -c "$f" -o "$o" &
     pids+=($!)
   fi
 done
 for p in "${pids[@]:-}"; do [ -n "$p" ] && wait "$p"; done
-$NVCC -shared -gencode arch=compute_100a,code=sm_100a -o lib/libmpmk.so build/*.o
-echo "built lib/libmpmk.so"
+$NVCC -shared -gencode arch=compute_100a,code=sm_100a -o "$OUT" "$BUILD"/*.o
+echo "built $OUT"

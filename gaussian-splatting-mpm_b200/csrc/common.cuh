@@ -37,6 +37,7 @@ struct mpmk_ctx {
     int cur;           // which set holds the current state
     int key_bits;
     int sm_count;
+    int g2p_ctas_per_sm, p2g_ctas_per_sm;  // occupancy-derived persistent grid sizes
     mpmk_bindings b;
     bool bound;
     mpmk_params prm;
@@ -133,3 +134,4 @@ int mpmk_launch_p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaSt
 int mpmk_launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);
 int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s);
 int mpmk_p2g_init(mpmk_ctx* ctx);
+int mpmk_g2p_init(mpmk_ctx* ctx);

@@ -5,7 +5,8 @@
 // for the strict-Q3 foam branch.  Stress is returned symmetrised (utils.py:52) as 6 floats
 // {00,01,02,11,12,22}.
 #pragma once
-#include "common.cuh"
+#include "../../include/mpmk.h"
+#include "devmath.cuh"
 #include "svd3.cuh"
 
 struct ConstParams {
@@ -15,7 +16,7 @@ struct ConstParams {
 };
 
 // tau = U diag(t) U^T
-__device__ __forceinline__ void sym_from_u(const float* U, const float* t, float* s6) {
+MPMK_DEV void sym_from_u(const float* U, const float* t, float* s6) {
     s6[0] = U[0] * t[0] * U[0] + U[1] * t[1] * U[1] + U[2] * t[2] * U[2];
     s6[1] = U[0] * t[0] * U[3] + U[1] * t[1] * U[4] + U[2] * t[2] * U[5];
     s6[2] = U[0] * t[0] * U[6] + U[1] * t[1] * U[7] + U[2] * t[2] * U[8];
@@ -25,7 +26,7 @@ __device__ __forceinline__ void sym_from_u(const float* U, const float* t, float
 }
 
 // F = U diag(d) V^T
-__device__ __forceinline__ void u_diag_vt(const float* U, const float* d, const float* V, float* F) {
+MPMK_DEV void u_diag_vt(const float* U, const float* d, const float* V, float* F) {
 #pragma unroll
     for (int r = 0; r < 3; ++r)
 #pragma unroll
@@ -34,7 +35,7 @@ __device__ __forceinline__ void u_diag_vt(const float* U, const float* d, const 
 }
 
 // constitutive_models.py:24-38 with V^T F^T = diag(sigma) U^T folded in: t_i = (2 mu eps_i + lam tr eps) sigma_i
-__device__ __forceinline__ void stvk_principal(const float* sig, float mu, float lam, float* t) {
+MPMK_DEV void stvk_principal(const float* sig, float mu, float lam, float* t) {
     float e0 = logf(fmaxf(sig[0], 0.01f)), e1 = logf(fmaxf(sig[1], 0.01f)), e2 = logf(fmaxf(sig[2], 0.01f));
     float tr = e0 + e1 + e2;
     t[0] = (2.0f * mu * e0 + lam * tr) * sig[0];
@@ -44,12 +45,11 @@ __device__ __forceinline__ void stvk_principal(const float* sig, float mu, float
 
 // Ft: trial deformation gradient (row-major 9).  Out: F (post return mapping), stress6.  mu/lam/ys are
 // per-particle and may be updated (metal hardening :96-97, plasticine softening).
-__device__ __forceinline__ void constitutive_update(const float* Ft, int mat, float& mu, float& lam, float& ys,
+MPMK_DEV void constitutive_update(const float* Ft, int mat, float& mu, float& lam, float& ys,
                                                     float dt, const ConstParams& P, float* F, float* s6) {
-    float U[9], V[9], sg[3];
-    svd3(Ft, U, sg, V);
 #pragma unroll
     for (int i = 0; i < 9; ++i) F[i] = Ft[i];
+    float U[9], V[9], sg[3];
     float t[3] = {0.0f, 0.0f, 0.0f};
 
     if (mat == MPMK_MAT_JELLY) {
@@ -58,11 +58,19 @@ __device__ __forceinline__ void constitutive_update(const float* Ft, int mat, fl
 #pragma unroll
             for (int i = 0; i < 6; ++i) s6[i] = 0.0f;
         } else {
-            // constitutive_models.py:11-20: tau = 2 mu (F - R) F^T + lam J (J-1) I, R = U V^T
-            float R[9], one[3] = {1.0f, 1.0f, 1.0f};
-            u_diag_vt(U, one, V, R);
-            float J = F[0] * (F[4] * F[8] - F[5] * F[7]) - F[1] * (F[3] * F[8] - F[5] * F[6]) +
-                      F[2] * (F[3] * F[7] - F[4] * F[6]);
+            // constitutive_models.py:11-20: tau = 2 mu (F - R) F^T + lam J (J-1) I, R = U V^T.  Only the
+            // rotation is needed: Newton polar iteration when det F > 0, the SVD otherwise (inverted
+            // element: sigma_3 < 0 under ti.svd's convention, U V^T stays a proper rotation).
+            float R[9];
+            const float J = F[0] * (F[4] * F[8] - F[5] * F[7]) - F[1] * (F[3] * F[8] - F[5] * F[6]) +
+                            F[2] * (F[3] * F[7] - F[4] * F[6]);
+            bool have_R = false;
+            if (J > 1e-6f) have_R = polar3(F, R);
+            if (!have_R) {
+                const float one[3] = {1.0f, 1.0f, 1.0f};
+                svd3(Ft, U, sg, V);
+                u_diag_vt(U, one, V, R);
+            }
             float D[9];
 #pragma unroll
             for (int i = 0; i < 9; ++i) D[i] = 2.0f * mu * (F[i] - R[i]);
@@ -71,12 +79,14 @@ __device__ __forceinline__ void constitutive_update(const float* Ft, int mat, fl
             for (int r = 0; r < 3; ++r)
 #pragma unroll
                 for (int c = 0; c < 3; ++c) M[3 * r + c] = D[3 * r] * F[3 * c] + D[3 * r + 1] * F[3 * c + 1] + D[3 * r + 2] * F[3 * c + 2];
-            float iso = lam * J * (J - 1.0f);
+            const float iso = lam * J * (J - 1.0f);
             s6[0] = M[0] + iso; s6[3] = M[4] + iso; s6[5] = M[8] + iso;
             s6[1] = 0.5f * (M[1] + M[3]); s6[2] = 0.5f * (M[2] + M[6]); s6[4] = 0.5f * (M[5] + M[7]);
         }
         return;
     }
+
+    svd3(Ft, U, sg, V);
 
     if (mat == MPMK_MAT_METAL || mat == MPMK_MAT_PLASTICINE) {
         // constitutive_models.py:63-103 (metal); plasticine = same with softening (unpinned)

@@ -22,6 +22,7 @@ struct G2PArgs {
     int4* ometa;
     float4 *ft0, *ft1, *ft2;
     uint32_t* okeys;
+    const uint4* items;
     const float4* grid_out;
     DevCounters* cnt;
     int64_t n;
@@ -36,142 +37,179 @@ __device__ __forceinline__ void bspline(float f, float* w, float* dw) {
     dw[0] = f - 1.5f; dw[1] = -2.0f * (f - 1.0f); dw[2] = f - 0.5f;
 }
 
-__global__ void __launch_bounds__(128) k_g2p(const G2PArgs a) {
-    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= a.n) return;
-    const uint32_t p = a.perm[r];
-    const uint32_t key = a.skeys[r];
-    const float4 X = ldg4(a.xm + p);
-    const int n = a.n_grid;
-    const uint32_t tile = key >> 6;
-    const int tz = tile % a.nt, ty = (tile / a.nt) % a.nt, tx = tile / (a.nt * a.nt);
-    const int bx = 4 * tx + ((key >> 4) & 3), by = 4 * ty + ((key >> 2) & 3), bz = 4 * tz + (key & 3);
-    const float fx = __fmul_rn(X.x, a.inv_dx) - (float)bx;
-    const float fy = __fmul_rn(X.y, a.inv_dx) - (float)by;
-    const float fz = __fmul_rn(X.z, a.inv_dx) - (float)bz;
-    float wx[3], wy[3], wz[3], dwx[3], dwy[3], dwz[3];
-    bspline(fx, wx, dwx); bspline(fy, wy, dwy); bspline(fz, wz, dwz);
-    // w_d (off_d - f_d): the APIC moment weights, shifted per axis so no large terms cancel
-    const float wxd[3] = {wx[0] * (0.f - fx), wx[1] * (1.f - fx), wx[2] * (2.f - fx)};
-    const float wyd[3] = {wy[0] * (0.f - fy), wy[1] * (1.f - fy), wy[2] * (2.f - fy)};
-    const float wzd[3] = {wz[0] * (0.f - fz), wz[1] * (1.f - fz), wz[2] * (2.f - fz)};
+// One warp per work item (<= MPMK_ITEM_MAX sorted particles of one 4x4x4-cell tile): the 6x6x6 nodes
+// the tile's stencils reach are staged once in the warp's shared-memory tile, then lanes = particles
+// gather from it in batches of 32.  The permutation/key of the next batch are fetched one batch ahead
+// so that each batch pays one global latency (particle records), not two.
+#ifndef G2P_WARPS
+#define G2P_WARPS 8
+#endif
+#ifndef G2P_MIN_CTAS
+#define G2P_MIN_CTAS 3
+#endif
 
-    // sums over the stencil: v, M_d = sum w (off_d - f_d) v (d=x,y,z), G_d = sum (dw_d-weighted) v
-    float v[3] = {0, 0, 0}, Mx[3] = {0, 0, 0}, My[3] = {0, 0, 0}, Mz[3] = {0, 0, 0};
-    float Gx[3] = {0, 0, 0}, Gy[3] = {0, 0, 0}, Gz[3] = {0, 0, 0};
-    const float4* g = a.grid_out + (((size_t)bx * n + by) * n + bz);
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-        float A[3] = {0, 0, 0}, Ay[3] = {0, 0, 0}, Gyi[3] = {0, 0, 0}, Az[3] = {0, 0, 0}, Gzi[3] = {0, 0, 0};
-#pragma unroll
-        for (int j = 0; j < 3; ++j) {
-            const float4* row = g + ((size_t)i * n + j) * n;
-            const float4 g0 = ldg4(row), g1 = ldg4(row + 1), g2 = ldg4(row + 2);
-            // contraction along z
-            const float ax = wz[0] * g0.x + wz[1] * g1.x + wz[2] * g2.x;
-            const float ay = wz[0] * g0.y + wz[1] * g1.y + wz[2] * g2.y;
-            const float az = wz[0] * g0.z + wz[1] * g1.z + wz[2] * g2.z;
-            const float zx = wzd[0] * g0.x + wzd[1] * g1.x + wzd[2] * g2.x;  // sum_k wz_k (k - fz) v
-            const float zy = wzd[0] * g0.y + wzd[1] * g1.y + wzd[2] * g2.y;
-            const float zz = wzd[0] * g0.z + wzd[1] * g1.z + wzd[2] * g2.z;
-            const float dx_ = dwz[0] * g0.x + dwz[1] * g1.x + dwz[2] * g2.x;
-            const float dy_ = dwz[0] * g0.y + dwz[1] * g1.y + dwz[2] * g2.y;
-            const float dz_ = dwz[0] * g0.z + dwz[1] * g1.z + dwz[2] * g2.z;
-            // contraction along y
-            const float wj = wy[j], wjj = wyd[j], dj = dwy[j];
-            A[0] += wj * ax; A[1] += wj * ay; A[2] += wj * az;
-            Ay[0] += wjj * ax; Ay[1] += wjj * ay; Ay[2] += wjj * az;
-            Gyi[0] += dj * ax; Gyi[1] += dj * ay; Gyi[2] += dj * az;
-            Az[0] += wj * zx; Az[1] += wj * zy; Az[2] += wj * zz;
-            Gzi[0] += wj * dx_; Gzi[1] += wj * dy_; Gzi[2] += wj * dz_;
-        }
-        // contraction along x
-        const float wi = wx[i], wii = wxd[i], di = dwx[i];
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            v[c] += wi * A[c];
-            Mx[c] += wii * A[c];
-            Gx[c] += di * A[c];
-            My[c] += wi * Ay[c];
-            Gy[c] += wi * Gyi[c];
-            Mz[c] += wi * Az[c];
-            Gz[c] += wi * Gzi[c];
-        }
-    }
-    // utils.py:266-275: v, x, C = sum w v (x) (off - f) * 4 inv_dx
+__global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PArgs a) {
+    __shared__ float4 tiles[G2P_WARPS][MPMK_TILE_NODES];
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    float4* tile = tiles[warp];
+    const uint32_t n_items = a.cnt->n_items;
+    const int n = a.n_grid;
     const float dt = a.dt;
-    const float nx = X.x + dt * v[0], ny = X.y + dt * v[1], nz = X.z + dt * v[2];
     const float k4 = 4.0f * a.inv_dx;
-    float C[9];
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-        C[3 * c + 0] = Mx[c] * k4;
-        C[3 * c + 1] = My[c] * k4;
-        C[3 * c + 2] = Mz[c] * k4;
-    }
-    // grad v = sum v (x) dweight  (row = velocity component, column = derivative direction)
-    float gv[9];
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-        gv[3 * c + 0] = Gx[c] * a.inv_dx;
-        gv[3 * c + 1] = Gy[c] * a.inv_dx;
-        gv[3 * c + 2] = Gz[c] * a.inv_dx;
-    }
-    // F_trial = (I + dt grad v) F   (utils.py:276-279)
-    const float4 F0 = ldg4(a.f0 + p), F1 = ldg4(a.f1 + p), F2 = ldg4(a.f2 + p);
-    const int4 meta = __ldg(a.meta + p);
-    const float Fo[9] = {F0.x, F0.y, F0.z, F0.w, F1.x, F1.y, F1.z, F1.w, F2.x};
-    float Ft[9];
-#pragma unroll
-    for (int rr = 0; rr < 3; ++rr)
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            float s = (rr == 0 ? 1.0f + dt * gv[0] : dt * gv[3 * rr + 0]) * Fo[c];
-            s += (rr == 1 ? 1.0f + dt * gv[4] : dt * gv[3 * rr + 1]) * Fo[3 + c];
-            s += (rr == 2 ? 1.0f + dt * gv[8] : dt * gv[3 * rr + 2]) * Fo[6 + c];
-            Ft[3 * rr + c] = s;
+
+    while (true) {
+        uint32_t it = 0;
+        if (lane == 0) it = atomicAdd(&a.cnt->g2p_cursor, 1u);
+        it = __shfl_sync(0xffffffffu, it, 0);
+        if (it >= n_items) break;
+        const uint4 item = a.items[it];
+        const int tz = item.z % a.nt, ty = (item.z / a.nt) % a.nt, tx = item.z / (a.nt * a.nt);
+        // first batch's permutation entries, in flight while the tile is staged
+        uint32_t p_next = 0, key_next = 0;
+        if ((uint32_t)lane < item.y) { p_next = a.perm[item.x + lane]; key_next = a.skeys[item.x + lane]; }
+        __syncwarp();  // previous item's gathers are done before the tile is overwritten
+        for (int i = lane; i < MPMK_TILE_NODES; i += 32) {
+            const int gx = 4 * tx + i / 36, gy = 4 * ty + (i / 6) % 6, gz = 4 * tz + i % 6;
+            float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (gx < n && gy < n && gz < n) g = ldg4(a.grid_out + (((size_t)gx * n + gy) * n + gz));
+            tile[i] = g;
         }
-    if (a.cp.flags & MPMK_WRITE_FTRIAL) {
-        a.ft0[r] = make_float4(Ft[0], Ft[1], Ft[2], Ft[3]);
-        a.ft1[r] = make_float4(Ft[4], Ft[5], Ft[6], Ft[7]);
-        a.ft2[r] = make_float4(Ft[8], 0.f, 0.f, 0.f);
-    }
-    if (a.cp.flags & MPMK_TRACK_COV) {
-        // update_cov, utils.py:187-215: cov += dt (grad_v cov + cov grad_v^T)
-        const float4 q0 = ldg4(a.cv0 + p), q1 = ldg4(a.cv1 + p);
-        const float cn[9] = {q0.x, q0.y, q0.z, q0.y, q0.w, q1.x, q0.z, q1.x, q1.y};
-        float o[9];
+        __syncwarp();
+
+        for (uint32_t b0 = 0; b0 < item.y; b0 += 32) {
+            const uint32_t p = p_next, key = key_next;
+            const bool active = b0 + lane < item.y;
+            const uint32_t r = item.x + b0 + lane;
+            if (b0 + 32 + lane < item.y) { p_next = a.perm[r + 32]; key_next = a.skeys[r + 32]; }
+            if (!active) continue;
+            const float4 X = ldg4(a.xm + p);
+            const float4 F0 = ldg4(a.f0 + p), F1 = ldg4(a.f1 + p), F2 = ldg4(a.f2 + p);
+            const int4 meta = __ldg(a.meta + p);
+            const int lx = (key >> 4) & 3, ly = (key >> 2) & 3, lz = key & 3;
+            const float fx = __fmul_rn(X.x, a.inv_dx) - (float)(4 * tx + lx);
+            const float fy = __fmul_rn(X.y, a.inv_dx) - (float)(4 * ty + ly);
+            const float fz = __fmul_rn(X.z, a.inv_dx) - (float)(4 * tz + lz);
+            float wx[3], wy[3], wz[3], dwx[3], dwy[3], dwz[3];
+            bspline(fx, wx, dwx); bspline(fy, wy, dwy); bspline(fz, wz, dwz);
+            // w_d (off_d - f_d): the APIC moment weights, shifted per axis so no large terms cancel
+            const float wxd[3] = {wx[0] * (0.f - fx), wx[1] * (1.f - fx), wx[2] * (2.f - fx)};
+            const float wyd[3] = {wy[0] * (0.f - fy), wy[1] * (1.f - fy), wy[2] * (2.f - fy)};
+            const float wzd[3] = {wz[0] * (0.f - fz), wz[1] * (1.f - fz), wz[2] * (2.f - fz)};
+
+            // sums over the stencil: v, M_d = sum w (off_d - f_d) v (d=x,y,z), G_d = sum (dw_d-weighted) v
+            float v[3] = {0, 0, 0}, Mx[3] = {0, 0, 0}, My[3] = {0, 0, 0}, Mz[3] = {0, 0, 0};
+            float Gx[3] = {0, 0, 0}, Gy[3] = {0, 0, 0}, Gz[3] = {0, 0, 0};
+            const float4* g = tile + (lx * 36 + ly * 6 + lz);
 #pragma unroll
-        for (int rr = 0; rr < 3; ++rr)
+            for (int i = 0; i < 3; ++i) {
+                float A[3] = {0, 0, 0}, Ay[3] = {0, 0, 0}, Gyi[3] = {0, 0, 0}, Az[3] = {0, 0, 0}, Gzi[3] = {0, 0, 0};
+#pragma unroll
+                for (int j = 0; j < 3; ++j) {
+                    const float4* row = g + (i * 36 + j * 6);
+                    const float4 g0 = row[0], g1 = row[1], g2 = row[2];
+                    // contraction along z
+                    const float ax = wz[0] * g0.x + wz[1] * g1.x + wz[2] * g2.x;
+                    const float ay = wz[0] * g0.y + wz[1] * g1.y + wz[2] * g2.y;
+                    const float az = wz[0] * g0.z + wz[1] * g1.z + wz[2] * g2.z;
+                    const float zx = wzd[0] * g0.x + wzd[1] * g1.x + wzd[2] * g2.x;  // sum_k wz_k (k - fz) v
+                    const float zy = wzd[0] * g0.y + wzd[1] * g1.y + wzd[2] * g2.y;
+                    const float zz = wzd[0] * g0.z + wzd[1] * g1.z + wzd[2] * g2.z;
+                    const float dx_ = dwz[0] * g0.x + dwz[1] * g1.x + dwz[2] * g2.x;
+                    const float dy_ = dwz[0] * g0.y + dwz[1] * g1.y + dwz[2] * g2.y;
+                    const float dz_ = dwz[0] * g0.z + dwz[1] * g1.z + dwz[2] * g2.z;
+                    // contraction along y
+                    const float wj = wy[j], wjj = wyd[j], dj = dwy[j];
+                    A[0] += wj * ax; A[1] += wj * ay; A[2] += wj * az;
+                    Ay[0] += wjj * ax; Ay[1] += wjj * ay; Ay[2] += wjj * az;
+                    Gyi[0] += dj * ax; Gyi[1] += dj * ay; Gyi[2] += dj * az;
+                    Az[0] += wj * zx; Az[1] += wj * zy; Az[2] += wj * zz;
+                    Gzi[0] += wj * dx_; Gzi[1] += wj * dy_; Gzi[2] += wj * dz_;
+                }
+                // contraction along x
+                const float wi = wx[i], wii = wxd[i], di = dwx[i];
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    v[c] += wi * A[c];
+                    Mx[c] += wii * A[c];
+                    Gx[c] += di * A[c];
+                    My[c] += wi * Ay[c];
+                    Gy[c] += wi * Gyi[c];
+                    Mz[c] += wi * Az[c];
+                    Gz[c] += wi * Gzi[c];
+                }
+            }
+            // utils.py:266-275: v, x, C = sum w v (x) (off - f) * 4 inv_dx
+            const float nx = X.x + dt * v[0], ny = X.y + dt * v[1], nz = X.z + dt * v[2];
+            float C[9];
 #pragma unroll
             for (int c = 0; c < 3; ++c) {
-                float s1 = gv[3 * rr] * cn[c] + gv[3 * rr + 1] * cn[3 + c] + gv[3 * rr + 2] * cn[6 + c];
-                float s2 = cn[3 * rr] * gv[3 * c] + cn[3 * rr + 1] * gv[3 * c + 1] + cn[3 * rr + 2] * gv[3 * c + 2];
-                o[3 * rr + c] = cn[3 * rr + c] + dt * (s1 + s2);
+                C[3 * c + 0] = Mx[c] * k4;
+                C[3 * c + 1] = My[c] * k4;
+                C[3 * c + 2] = Mz[c] * k4;
             }
-        a.ocv0[r] = make_float4(o[0], o[1], o[2], o[4]);
-        a.ocv1[r] = make_float4(o[5], o[8], 0.f, 0.f);
+            // grad v = sum v (x) dweight  (row = velocity component, column = derivative direction)
+            float gv[9];
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                gv[3 * c + 0] = Gx[c] * a.inv_dx;
+                gv[3 * c + 1] = Gy[c] * a.inv_dx;
+                gv[3 * c + 2] = Gz[c] * a.inv_dx;
+            }
+            // F_trial = (I + dt grad v) F   (utils.py:276-279)
+            const float Fo[9] = {F0.x, F0.y, F0.z, F0.w, F1.x, F1.y, F1.z, F1.w, F2.x};
+            float Ft[9];
+#pragma unroll
+            for (int rr = 0; rr < 3; ++rr)
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    float s = (rr == 0 ? 1.0f + dt * gv[0] : dt * gv[3 * rr + 0]) * Fo[c];
+                    s += (rr == 1 ? 1.0f + dt * gv[4] : dt * gv[3 * rr + 1]) * Fo[3 + c];
+                    s += (rr == 2 ? 1.0f + dt * gv[8] : dt * gv[3 * rr + 2]) * Fo[6 + c];
+                    Ft[3 * rr + c] = s;
+                }
+            if (a.cp.flags & MPMK_WRITE_FTRIAL) {
+                a.ft0[r] = make_float4(Ft[0], Ft[1], Ft[2], Ft[3]);
+                a.ft1[r] = make_float4(Ft[4], Ft[5], Ft[6], Ft[7]);
+                a.ft2[r] = make_float4(Ft[8], 0.f, 0.f, 0.f);
+            }
+            if (a.cp.flags & MPMK_TRACK_COV) {
+                // update_cov, utils.py:187-215: cov += dt (grad_v cov + cov grad_v^T)
+                const float4 q0 = ldg4(a.cv0 + p), q1 = ldg4(a.cv1 + p);
+                const float cn[9] = {q0.x, q0.y, q0.z, q0.y, q0.w, q1.x, q0.z, q1.x, q1.y};
+                float o[9];
+#pragma unroll
+                for (int rr = 0; rr < 3; ++rr)
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        float s1 = gv[3 * rr] * cn[c] + gv[3 * rr + 1] * cn[3 + c] + gv[3 * rr + 2] * cn[6 + c];
+                        float s2 = cn[3 * rr] * gv[3 * c] + cn[3 * rr + 1] * gv[3 * c + 1] + cn[3 * rr + 2] * gv[3 * c + 2];
+                        o[3 * rr + c] = cn[3 * rr + c] + dt * (s1 + s2);
+                    }
+                a.ocv0[r] = make_float4(o[0], o[1], o[2], o[4]);
+                a.ocv1[r] = make_float4(o[5], o[8], 0.f, 0.f);
+            }
+            a.oxm[r] = make_float4(nx, ny, nz, X.w);
+            a.ovv[r] = make_float4(v[0], v[1], v[2], 0.f);
+            a.oc0[r] = make_float4(C[0], C[1], C[2], C[3]);
+            a.oc1[r] = make_float4(C[4], C[5], C[6], C[7]);
+            bool cl = false;
+            const int kx = base_cell(nx, a.inv_dx, n, cl), ky = base_cell(ny, a.inv_dx, n, cl), kz = base_cell(nz, a.inv_dx, n, cl);
+            a.okeys[r] = make_key(kx, ky, kz, a.nt);
+            if (cl) atomicAdd(&a.cnt->n_clamped, 1u);
+            a.ometa[r] = meta;
+            // constitutive update for the next substep
+            float mu = F2.y, lam = F2.z, ys = F2.w;
+            float Fn[9], s6[6];
+            constitutive_update(Ft, meta.y, mu, lam, ys, dt, a.cp, Fn, s6);
+            const float vol = __int_as_float(meta.z);
+            a.ocs[r] = make_float4(C[8], s6[0], s6[1], s6[2]);
+            a.os1[r] = make_float4(s6[3], s6[4], s6[5], vol);
+            a.of0[r] = make_float4(Fn[0], Fn[1], Fn[2], Fn[3]);
+            a.of1[r] = make_float4(Fn[4], Fn[5], Fn[6], Fn[7]);
+            a.of2[r] = make_float4(Fn[8], mu, lam, ys);
+        }
     }
-    // constitutive update for the next substep
-    float mu = F2.y, lam = F2.z, ys = F2.w;
-    float Fn[9], s6[6];
-    constitutive_update(Ft, meta.y, mu, lam, ys, dt, a.cp, Fn, s6);
-
-    const float vol = __int_as_float(meta.z);
-    a.oxm[r] = make_float4(nx, ny, nz, X.w);
-    a.ovv[r] = make_float4(v[0], v[1], v[2], 0.f);
-    a.oc0[r] = make_float4(C[0], C[1], C[2], C[3]);
-    a.oc1[r] = make_float4(C[4], C[5], C[6], C[7]);
-    a.ocs[r] = make_float4(C[8], s6[0], s6[1], s6[2]);
-    a.os1[r] = make_float4(s6[3], s6[4], s6[5], vol);
-    a.of0[r] = make_float4(Fn[0], Fn[1], Fn[2], Fn[3]);
-    a.of1[r] = make_float4(Fn[4], Fn[5], Fn[6], Fn[7]);
-    a.of2[r] = make_float4(Fn[8], mu, lam, ys);
-    a.ometa[r] = meta;
-    bool cl = false;
-    const int kx = base_cell(nx, a.inv_dx, n, cl), ky = base_cell(ny, a.inv_dx, n, cl), kz = base_cell(nz, a.inv_dx, n, cl);
-    a.okeys[r] = make_key(kx, ky, kz, a.nt);
-    if (cl) atomicAdd(&a.cnt->n_clamped, 1u);
 }
 
 // utils.py:14-54 on the current set in place (init, and after from_torch edits of F)
@@ -200,6 +238,13 @@ static ConstParams make_cp(const mpmk_ctx* ctx) {
     return cp;
 }
 
+int mpmk_g2p_init(mpmk_ctx* ctx) {
+    int per_sm = 0;
+    MPMK_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_g2p, G2P_WARPS * 32, 0));
+    ctx->g2p_ctas_per_sm = per_sm > 0 ? per_sm : 1;
+    return 0;
+}
+
 int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s) {
     if (!ctx->prepared) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_g2p: sort + prepare_grid first");
     const int src = ctx->cur, dst = 1 - ctx->cur;
@@ -214,6 +259,7 @@ int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s) {
         a.os1 = (float4*)B.s1; a.of0 = (float4*)B.f0; a.of1 = (float4*)B.f1; a.of2 = (float4*)B.f2;
         a.ocv0 = (float4*)B.cv0; a.ocv1 = (float4*)B.cv1; a.ometa = (int4*)B.meta;
         a.ft0 = (float4*)ctx->b.ft0; a.ft1 = (float4*)ctx->b.ft1; a.ft2 = (float4*)ctx->b.ft2;
+        a.items = ctx->items;
         a.okeys = (uint32_t*)ctx->b.keys; a.grid_out = (const float4*)ctx->b.grid_out; a.cnt = ctx->counters;
         a.n = ctx->n; a.n_grid = ctx->n_grid; a.nt = ctx->nt; a.inv_dx = ctx->inv_dx; a.dt = dt;
         a.cp = make_cp(ctx);
@@ -221,7 +267,10 @@ int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s) {
             MPMK_FAIL(ctx, MPMK_ERR_STATE, "MPMK_TRACK_COV needs cv0/cv1 bound");
         if ((a.cp.flags & MPMK_WRITE_FTRIAL) && (!a.ft0 || !a.ft1 || !a.ft2))
             MPMK_FAIL(ctx, MPMK_ERR_STATE, "MPMK_WRITE_FTRIAL needs ft0..ft2 bound");
-        k_g2p<<<div_up(ctx->n, 128), 128, 0, s>>>(a);
+        // persistent grid, warps fetch work items dynamically (counters->g2p_cursor, zeroed by prepare)
+        int64_t want = (ctx->n / 32 + G2P_WARPS - 1) / G2P_WARPS + 1;
+        int64_t cap = (int64_t)ctx->sm_count * ctx->g2p_ctas_per_sm;
+        k_g2p<<<(int)(want < cap ? want : cap), G2P_WARPS * 32, 0, s>>>(a);
         MPMK_LAUNCH_CHECK(ctx);
     }
     ctx->cur = dst;

@@ -7,15 +7,22 @@
 //     weights, and the tensor-product partial sums
 //         Y_ij = wy_j (wx_i (q + i A0) + dwx_i S0) + wx_i (wy_j j A1 + dwy_j S1),   R_k = wz_k k A2 + dwz_k S2
 //     with A = m C dx, S = -dt vol inv_dx stress, q = m v - A fx, staged in shared memory;
+//     (R_k is stored divided by the particle mass and Y_ij carries m wx_i wy_j in its 4th lane);
 //   phase B (lane = stencil node (i,j,k)): walks the batch in sorted order; node value
-//         wz_k Y_ij + (wx_i wy_j) R_k,  mass m wx_i wy_j wz_k
-//     accumulates in registers while consecutive particles share a cell (the groups
-//     __match_any_sync finds in phase A) and is added to the shared tile once per (cell run, node):
-//     no shared-memory atomics, every lane owns a distinct node.
+//         wz_k Y_ij + (m wx_i wy_j) R_k / m,  mass (m wx_i wy_j) wz_k
+//     accumulates in registers while consecutive particles share a cell -- the runs are the groups
+//     __match_any_sync finds in phase A, their heads collected with one ballot per batch -- and is
+//     added to the shared tile once per (cell run, node): no shared-memory atomics, every lane owns a
+//     distinct node.
 // The tile is flushed with one 16-byte red.global.add.v4.f32 per non-zero node.
 #include "common.cuh"
 
-#define P2G_WARPS 8
+#ifndef P2G_WARPS
+#define P2G_WARPS 4
+#endif
+#ifndef P2G_MIN_CTAS
+#define P2G_MIN_CTAS 5
+#endif
 #define P2G_REC_STRIDE 33  // float4 per record slot: 32 lanes + 1 pad (bank-conflict-free phase B reads)
 #define P2G_REC_SLOTS 12   // 9 x {Y_ij.xyz, wx_i wy_j} + 3 x {R_k.xyz, wz_k}
 
@@ -37,7 +44,7 @@ struct P2GArgs {
     mpmk_impulse imp[MPMK_MAX_IMPULSES];
 };
 
-__global__ void __launch_bounds__(P2G_WARPS * 32, 2) k_p2g(const P2GArgs a) {
+__global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GArgs a) {
     extern __shared__ float4 smem_raw[];
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -64,8 +71,7 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, 2) k_p2g(const P2GArgs a) {
 
         for (uint32_t b0 = 0; b0 < item.y; b0 += 32) {
             const int nbatch = min(32u, item.y - b0);
-            int my_cell = 0;
-            float my_m = 0.f;
+            int my_cell = 64;  // lanes past the end of the batch never match a real cell
             // ---------------- phase A: lane = particle ----------------
             if (lane < nbatch) {
                 const uint32_t r = item.x + b0 + lane;
@@ -76,7 +82,7 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, 2) k_p2g(const P2GArgs a) {
                 my_cell = key & 63;
                 const int lx = my_cell >> 4, ly = (my_cell >> 2) & 3, lz = my_cell & 3;
                 const float m = X.w, vol = S1.w;
-                my_m = m;
+                const float inv_m = m > 0.f ? __frcp_rn(m) : 0.f;
                 float vx = V.x, vy = V.y, vz = V.z;
                 for (int q = 0; q < a.n_imp; ++q) {
                     const mpmk_impulse& im = a.imp[q];
@@ -132,7 +138,7 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, 2) k_p2g(const P2GArgs a) {
                         yw.x = wy[j] * X0 + wx[i] * T0[j];
                         yw.y = wy[j] * X1 + wx[i] * T1[j];
                         yw.z = wy[j] * X2 + wx[i] * T2[j];
-                        yw.w = wx[i] * wy[j];
+                        yw.w = m * (wx[i] * wy[j]);
                         S.rec[(i * 3 + j) * P2G_REC_STRIDE + lane] = yw;
                     }
                 }
@@ -140,40 +146,46 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, 2) k_p2g(const P2GArgs a) {
                 for (int k = 0; k < 3; ++k) {
                     const float wk = wz[k] * (float)k;
                     float4 rw;
-                    rw.x = wk * A02 + dwz[k] * S02;
-                    rw.y = wk * A12 + dwz[k] * S12;
-                    rw.z = wk * A22 + dwz[k] * S22;
+                    rw.x = (wk * A02 + dwz[k] * S02) * inv_m;
+                    rw.y = (wk * A12 + dwz[k] * S12) * inv_m;
+                    rw.z = (wk * A22 + dwz[k] * S22) * inv_m;
                     rw.w = wz[k];
                     S.rec[(9 + k) * P2G_REC_STRIDE + lane] = rw;
                 }
             }
             __syncwarp();
             // ---------------- phase B: lane = stencil node ----------------
+            // run heads: the lowest lane of each __match_any_sync group (lane 0 continues the run carried
+            // over from the previous batch when the cell is the same)
+            // (sorted input: the lanes sharing a cell are contiguous, so a run's head is its lowest peer)
+            const unsigned peers = __match_any_sync(0xffffffffu, my_cell);
+            const bool head = (lane < nbatch) && (lane == __ffs(peers) - 1) && !(lane == 0 && my_cell == cur_cell);
+            const unsigned heads = __ballot_sync(0xffffffffu, head);
             const float4* recY = S.rec + nij * P2G_REC_STRIDE;
             const float4* recR = S.rec + (9 + nk) * P2G_REC_STRIDE;
-#pragma unroll 4
-            for (int l = 0; l < nbatch; ++l) {
-                const int cell = __shfl_sync(0xffffffffu, my_cell, l);
-                const float m = __shfl_sync(0xffffffffu, my_m, l);
-                if (cell != cur_cell) {
-                    if (cur_cell >= 0) {
-                        __syncwarp();
-                        if (node_lane) {
-                            const int nd = (cur_cell >> 4) * 36 + ((cur_cell >> 2) & 3) * 6 + (cur_cell & 3) + noff;
-                            float4 t = S.tile[nd];
-                            t.x += acc.x; t.y += acc.y; t.z += acc.z; t.w += acc.w;
-                            S.tile[nd] = t;
-                        }
+            int l = 0;
+            while (l < nbatch) {
+                if ((heads >> l) & 1u) {
+                    if (cur_cell >= 0 && node_lane) {
+                        const int nd = (cur_cell >> 4) * 36 + ((cur_cell >> 2) & 3) * 6 + (cur_cell & 3) + noff;
+                        float4 t = S.tile[nd];
+                        t.x += acc.x; t.y += acc.y; t.z += acc.z; t.w += acc.w;
+                        S.tile[nd] = t;
                     }
                     acc = zero4;
-                    cur_cell = cell;
+                    cur_cell = __shfl_sync(0xffffffffu, my_cell, l);
                 }
-                const float4 yw = recY[l];
-                const float4 rw = recR[l];
-                acc.x += rw.w * yw.x + yw.w * rw.x;
-                acc.y += rw.w * yw.y + yw.w * rw.y;
-                acc.z += rw.w * yw.z + yw.w * rw.z;
-                acc.w += m * (yw.w * rw.w);
+                const unsigned rest = heads & ~((2u << l) - 1u);  // heads strictly after l
+                const int end = rest ? (__ffs(rest) - 1) : nbatch;
+#pragma unroll 4
+                for (; l < end; ++l) {
+                    const float4 yw = recY[l];
+                    const float4 rw = recR[l];
+                    acc.x += rw.w * yw.x + yw.w * rw.x;
+                    acc.y += rw.w * yw.y + yw.w * rw.y;
+                    acc.z += rw.w * yw.z + yw.w * rw.z;
+                    acc.w += yw.w * rw.w;
+                }
             }
             __syncwarp();
         }
@@ -215,15 +227,21 @@ int mpmk_launch_p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaSt
         memcpy(a.imp, ops->impulses, sizeof(mpmk_impulse) * ops->n_impulses);
     }
     const int smem = (int)sizeof(P2GWarpSmem) * P2G_WARPS;
-    // persistent grid: 2 CTAs per SM, warps fetch items dynamically
+    // persistent grid: as many CTAs as fit per SM, warps fetch items dynamically
     int64_t want = (ctx->n / 32 + P2G_WARPS - 1) / P2G_WARPS + 1;
-    int grid = (int)(want < (int64_t)ctx->sm_count * 2 ? want : (int64_t)ctx->sm_count * 2);
+    int64_t cap = (int64_t)ctx->sm_count * ctx->p2g_ctas_per_sm;
+    int grid = (int)(want < cap ? want : cap);
     k_p2g<<<grid, P2G_WARPS * 32, smem, s>>>(a);
     MPMK_LAUNCH_CHECK(ctx);
     return 0;
 }
 
 int mpmk_p2g_init(mpmk_ctx* ctx) {
-    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_p2g, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(P2GWarpSmem) * P2G_WARPS));
+    const int smem = (int)sizeof(P2GWarpSmem) * P2G_WARPS;
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_p2g, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_p2g, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    int per_sm = 0;
+    MPMK_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_p2g, P2G_WARPS * 32, smem));
+    ctx->p2g_ctas_per_sm = per_sm > 0 ? per_sm : 1;
     return 0;
 }

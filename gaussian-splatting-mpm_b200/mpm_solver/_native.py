@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(_ROOT, "lib", "libmpmk.so")
+# MPMK_LIB selects another build of the same library (kernel tuning experiments); default in-tree build
+LIB_PATH = os.environ.get("MPMK_LIB") or os.path.join(_ROOT, "lib", "libmpmk.so")
 
 MAT_JELLY, MAT_METAL, MAT_SAND, MAT_FOAM, MAT_FLUID, MAT_PLASTICINE = range(6)
 STRICT_Q1, STRICT_Q3, WRITE_FTRIAL, TRACK_COV = 1, 2, 4, 8
