@@ -126,6 +126,54 @@ __device__ __forceinline__ uint32_t make_key(int bx, int by, int bz, int nt) {
     return (tile << 6) | (uint32_t)(((bx & 3) << 4) | ((by & 3) << 2) | (bz & 3));
 }
 
+// ---- asynchronous global->shared copies (LDGSTS) and the batch stream shared by p2g and g2p ----
+__device__ __forceinline__ void cp_async16(void* smem, const void* gptr) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gptr) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+struct BatchDesc {
+    uint32_t base;  // first sorted index
+    uint32_t tile;
+    int count;      // 0 = end of stream
+    bool first;     // first batch of its item
+};
+
+// warp-uniform stream of batches over dynamically fetched work items
+struct BatchStream {
+    const uint4* items;
+    uint32_t* cursor;
+    uint32_t n_items;
+    uint4 item;
+    uint32_t off;
+    bool done;
+    __device__ __forceinline__ void init(const uint4* it, uint32_t* cur, uint32_t n) {
+        items = it; cursor = cur; n_items = n; item = make_uint4(0u, 0u, 0u, 0u); off = 0; done = false;
+    }
+    __device__ __forceinline__ BatchDesc next(int lane) {
+        BatchDesc d;
+        d.base = 0; d.tile = 0; d.count = 0; d.first = false;
+        if (done) return d;
+        if (off >= item.y) {
+            uint32_t it = 0;
+            if (lane == 0) it = atomicAdd(cursor, 1u);
+            it = __shfl_sync(0xffffffffu, it, 0);
+            if (it >= n_items) { done = true; return d; }
+            item = items[it];
+            off = 0;
+        }
+        d.base = item.x + off;
+        d.tile = item.z;
+        d.count = (int)min(32u, item.y - off);
+        d.first = (off == 0);
+        off += 32;
+        return d;
+    }
+};
+
 // internal launchers (one per translation unit)
 int mpmk_launch_keys(mpmk_ctx* ctx, cudaStream_t s);
 int mpmk_launch_sort(mpmk_ctx* ctx, cudaStream_t s);

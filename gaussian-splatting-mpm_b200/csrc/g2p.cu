@@ -37,55 +37,83 @@ __device__ __forceinline__ void bspline(float f, float* w, float* dw) {
     dw[0] = f - 1.5f; dw[1] = -2.0f * (f - 1.0f); dw[2] = f - 0.5f;
 }
 
-// One warp per work item (<= MPMK_ITEM_MAX sorted particles of one 4x4x4-cell tile): the 6x6x6 nodes
-// the tile's stencils reach are staged once in the warp's shared-memory tile, then lanes = particles
-// gather from it in batches of 32.  The permutation/key of the next batch are fetched one batch ahead
-// so that each batch pays one global latency (particle records), not two.
+// One warp per work item (<= MPMK_ITEM_MAX sorted particles of one 4x4x4-cell tile).  The 6x6x6 nodes the
+// tile's stencils reach are staged in the warp's shared-memory tile; lanes = particles gather from it
+// in batches of 32.  The kernel is latency-bound unless every warp keeps global loads in flight while it
+// computes (Little: ~40 KB per SM against 2.7 KB per batch), so the batches form a three-deep software
+// pipeline that also crosses item boundaries:
+//     batch C: permutation + key loads in flight (registers)
+//     batch B: particle records xm,f0,f1,f2,meta in flight (cp.async, 16 B per lane per array, into
+//              the other half of a double-buffered shared-memory stage)
+//     batch A: gather + C/F update + constitutive update + stores
 #ifndef G2P_WARPS
 #define G2P_WARPS 8
 #endif
 #ifndef G2P_MIN_CTAS
 #define G2P_MIN_CTAS 3
 #endif
+#define G2P_NREC 5
+
+struct __align__(16) G2PWarpSmem {
+    float4 rec[2][G2P_NREC][32];
+    float4 tile[MPMK_TILE_NODES];
+};
 
 __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PArgs a) {
-    __shared__ float4 tiles[G2P_WARPS][MPMK_TILE_NODES];
+    extern __shared__ float4 g2p_smem_raw[];
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    float4* tile = tiles[warp];
-    const uint32_t n_items = a.cnt->n_items;
+    G2PWarpSmem& S = reinterpret_cast<G2PWarpSmem*>(g2p_smem_raw)[warp];
     const int n = a.n_grid;
     const float dt = a.dt;
     const float k4 = 4.0f * a.inv_dx;
 
-    while (true) {
-        uint32_t it = 0;
-        if (lane == 0) it = atomicAdd(&a.cnt->g2p_cursor, 1u);
-        it = __shfl_sync(0xffffffffu, it, 0);
-        if (it >= n_items) break;
-        const uint4 item = a.items[it];
-        const int tz = item.z % a.nt, ty = (item.z / a.nt) % a.nt, tx = item.z / (a.nt * a.nt);
-        // first batch's permutation entries, in flight while the tile is staged
-        uint32_t p_next = 0, key_next = 0;
-        if ((uint32_t)lane < item.y) { p_next = a.perm[item.x + lane]; key_next = a.skeys[item.x + lane]; }
-        __syncwarp();  // previous item's gathers are done before the tile is overwritten
-        for (int i = lane; i < MPMK_TILE_NODES; i += 32) {
-            const int gx = 4 * tx + i / 36, gy = 4 * ty + (i / 6) % 6, gz = 4 * tz + i % 6;
-            float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (gx < n && gy < n && gz < n) g = ldg4(a.grid_out + (((size_t)gx * n + gy) * n + gz));
-            tile[i] = g;
+    BatchStream bs;
+    bs.init(a.items, &a.cnt->g2p_cursor, a.cnt->n_items);
+    BatchDesc dA = bs.next(lane);
+    if (dA.count == 0) return;
+    uint32_t pA = 0, kA = 0, pB = 0, kB = 0, pC = 0, kC = 0;
+    if (lane < dA.count) { pA = a.perm[dA.base + lane]; kA = a.skeys[dA.base + lane]; }
+    BatchDesc dB = bs.next(lane);
+    if (lane < dB.count) { pB = a.perm[dB.base + lane]; kB = a.skeys[dB.base + lane]; }
+    int stage = 0;
+    if (lane < dA.count) {
+        cp_async16(&S.rec[0][0][lane], a.xm + pA);
+        cp_async16(&S.rec[0][1][lane], a.f0 + pA);
+        cp_async16(&S.rec[0][2][lane], a.f1 + pA);
+        cp_async16(&S.rec[0][3][lane], a.f2 + pA);
+        cp_async16(&S.rec[0][4][lane], a.meta + pA);
+    }
+    cp_async_commit();
+
+    while (dA.count > 0) {
+        const int tz = dA.tile % a.nt, ty = (dA.tile / a.nt) % a.nt, tx = dA.tile / (a.nt * a.nt);
+        if (dA.first) {
+            // a new item: restage the node tile (the previous item's gathers ended with __syncwarp)
+            for (int i = lane; i < MPMK_TILE_NODES; i += 32) {
+                const int gx = 4 * tx + i / 36, gy = 4 * ty + (i / 6) % 6, gz = 4 * tz + i % 6;
+                if (gx < n && gy < n && gz < n) cp_async16(&S.tile[i], a.grid_out + (((size_t)gx * n + gy) * n + gz));
+                else S.tile[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
         }
+        cp_async_commit();
+        if (lane < dB.count) {
+            cp_async16(&S.rec[stage ^ 1][0][lane], a.xm + pB);
+            cp_async16(&S.rec[stage ^ 1][1][lane], a.f0 + pB);
+            cp_async16(&S.rec[stage ^ 1][2][lane], a.f1 + pB);
+            cp_async16(&S.rec[stage ^ 1][3][lane], a.f2 + pB);
+            cp_async16(&S.rec[stage ^ 1][4][lane], a.meta + pB);
+        }
+        cp_async_commit();
+        const BatchDesc dC = bs.next(lane);
+        if (lane < dC.count) { pC = a.perm[dC.base + lane]; kC = a.skeys[dC.base + lane]; }
+        cp_async_wait<1>();  // batch A's records and the tile have landed; batch B's may still be in flight
         __syncwarp();
 
-        for (uint32_t b0 = 0; b0 < item.y; b0 += 32) {
-            const uint32_t p = p_next, key = key_next;
-            const bool active = b0 + lane < item.y;
-            const uint32_t r = item.x + b0 + lane;
-            if (b0 + 32 + lane < item.y) { p_next = a.perm[r + 32]; key_next = a.skeys[r + 32]; }
-            if (!active) continue;
-            const float4 X = ldg4(a.xm + p);
-            const float4 F0 = ldg4(a.f0 + p), F1 = ldg4(a.f1 + p), F2 = ldg4(a.f2 + p);
-            const int4 meta = __ldg(a.meta + p);
+        if (lane < dA.count) {
+            const uint32_t r = dA.base + lane;
+            const uint32_t key = kA;
+            const float4 X = S.rec[stage][0][lane];
             const int lx = (key >> 4) & 3, ly = (key >> 2) & 3, lz = key & 3;
             const float fx = __fmul_rn(X.x, a.inv_dx) - (float)(4 * tx + lx);
             const float fy = __fmul_rn(X.y, a.inv_dx) - (float)(4 * ty + ly);
@@ -100,7 +128,7 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
             // sums over the stencil: v, M_d = sum w (off_d - f_d) v (d=x,y,z), G_d = sum (dw_d-weighted) v
             float v[3] = {0, 0, 0}, Mx[3] = {0, 0, 0}, My[3] = {0, 0, 0}, Mz[3] = {0, 0, 0};
             float Gx[3] = {0, 0, 0}, Gy[3] = {0, 0, 0}, Gz[3] = {0, 0, 0};
-            const float4* g = tile + (lx * 36 + ly * 6 + lz);
+            const float4* g = S.tile + (lx * 36 + ly * 6 + lz);
 #pragma unroll
             for (int i = 0; i < 3; ++i) {
                 float A[3] = {0, 0, 0}, Ay[3] = {0, 0, 0}, Gyi[3] = {0, 0, 0}, Az[3] = {0, 0, 0}, Gzi[3] = {0, 0, 0};
@@ -141,13 +169,15 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
             }
             // utils.py:266-275: v, x, C = sum w v (x) (off - f) * 4 inv_dx
             const float nx = X.x + dt * v[0], ny = X.y + dt * v[1], nz = X.z + dt * v[2];
-            float C[9];
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                C[3 * c + 0] = Mx[c] * k4;
-                C[3 * c + 1] = My[c] * k4;
-                C[3 * c + 2] = Mz[c] * k4;
-            }
+            a.oxm[r] = make_float4(nx, ny, nz, X.w);
+            a.ovv[r] = make_float4(v[0], v[1], v[2], 0.f);
+            bool cl = false;
+            const int kx = base_cell(nx, a.inv_dx, n, cl), ky = base_cell(ny, a.inv_dx, n, cl), kz = base_cell(nz, a.inv_dx, n, cl);
+            a.okeys[r] = make_key(kx, ky, kz, a.nt);
+            if (cl) atomicAdd(&a.cnt->n_clamped, 1u);
+            a.oc0[r] = make_float4(Mx[0] * k4, My[0] * k4, Mz[0] * k4, Mx[1] * k4);
+            a.oc1[r] = make_float4(My[1] * k4, Mz[1] * k4, Mx[2] * k4, My[2] * k4);
+            const float C22 = Mz[2] * k4;
             // grad v = sum v (x) dweight  (row = velocity component, column = derivative direction)
             float gv[9];
 #pragma unroll
@@ -157,6 +187,7 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
                 gv[3 * c + 2] = Gz[c] * a.inv_dx;
             }
             // F_trial = (I + dt grad v) F   (utils.py:276-279)
+            const float4 F0 = S.rec[stage][1][lane], F1 = S.rec[stage][2][lane], F2 = S.rec[stage][3][lane];
             const float Fo[9] = {F0.x, F0.y, F0.z, F0.w, F1.x, F1.y, F1.z, F1.w, F2.x};
             float Ft[9];
 #pragma unroll
@@ -175,7 +206,7 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
             }
             if (a.cp.flags & MPMK_TRACK_COV) {
                 // update_cov, utils.py:187-215: cov += dt (grad_v cov + cov grad_v^T)
-                const float4 q0 = ldg4(a.cv0 + p), q1 = ldg4(a.cv1 + p);
+                const float4 q0 = ldg4(a.cv0 + pA), q1 = ldg4(a.cv1 + pA);
                 const float cn[9] = {q0.x, q0.y, q0.z, q0.y, q0.w, q1.x, q0.z, q1.x, q1.y};
                 float o[9];
 #pragma unroll
@@ -189,27 +220,25 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
                 a.ocv0[r] = make_float4(o[0], o[1], o[2], o[4]);
                 a.ocv1[r] = make_float4(o[5], o[8], 0.f, 0.f);
             }
-            a.oxm[r] = make_float4(nx, ny, nz, X.w);
-            a.ovv[r] = make_float4(v[0], v[1], v[2], 0.f);
-            a.oc0[r] = make_float4(C[0], C[1], C[2], C[3]);
-            a.oc1[r] = make_float4(C[4], C[5], C[6], C[7]);
-            bool cl = false;
-            const int kx = base_cell(nx, a.inv_dx, n, cl), ky = base_cell(ny, a.inv_dx, n, cl), kz = base_cell(nz, a.inv_dx, n, cl);
-            a.okeys[r] = make_key(kx, ky, kz, a.nt);
-            if (cl) atomicAdd(&a.cnt->n_clamped, 1u);
+            const int4 meta = *reinterpret_cast<const int4*>(&S.rec[stage][4][lane]);
             a.ometa[r] = meta;
             // constitutive update for the next substep
             float mu = F2.y, lam = F2.z, ys = F2.w;
             float Fn[9], s6[6];
             constitutive_update(Ft, meta.y, mu, lam, ys, dt, a.cp, Fn, s6);
             const float vol = __int_as_float(meta.z);
-            a.ocs[r] = make_float4(C[8], s6[0], s6[1], s6[2]);
+            a.ocs[r] = make_float4(C22, s6[0], s6[1], s6[2]);
             a.os1[r] = make_float4(s6[3], s6[4], s6[5], vol);
             a.of0[r] = make_float4(Fn[0], Fn[1], Fn[2], Fn[3]);
             a.of1[r] = make_float4(Fn[4], Fn[5], Fn[6], Fn[7]);
             a.of2[r] = make_float4(Fn[8], mu, lam, ys);
         }
+        __syncwarp();  // all lanes are done with the tile and this stage before either is overwritten
+        dA = dB; pA = pB; kA = kB;
+        dB = dC; pB = pC; kB = kC;
+        stage ^= 1;
     }
+    cp_async_wait<0>();
 }
 
 // utils.py:14-54 on the current set in place (init, and after from_torch edits of F)
@@ -239,8 +268,11 @@ static ConstParams make_cp(const mpmk_ctx* ctx) {
 }
 
 int mpmk_g2p_init(mpmk_ctx* ctx) {
+    const int smem = (int)sizeof(G2PWarpSmem) * G2P_WARPS;
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_g2p, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_g2p, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     int per_sm = 0;
-    MPMK_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_g2p, G2P_WARPS * 32, 0));
+    MPMK_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_g2p, G2P_WARPS * 32, smem));
     ctx->g2p_ctas_per_sm = per_sm > 0 ? per_sm : 1;
     return 0;
 }
@@ -270,7 +302,7 @@ int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s) {
         // persistent grid, warps fetch work items dynamically (counters->g2p_cursor, zeroed by prepare)
         int64_t want = (ctx->n / 32 + G2P_WARPS - 1) / G2P_WARPS + 1;
         int64_t cap = (int64_t)ctx->sm_count * ctx->g2p_ctas_per_sm;
-        k_g2p<<<(int)(want < cap ? want : cap), G2P_WARPS * 32, 0, s>>>(a);
+        k_g2p<<<(int)(want < cap ? want : cap), G2P_WARPS * 32, sizeof(G2PWarpSmem) * G2P_WARPS, s>>>(a);
         MPMK_LAUNCH_CHECK(ctx);
     }
     ctx->cur = dst;

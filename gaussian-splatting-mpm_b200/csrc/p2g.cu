@@ -21,14 +21,17 @@
 #define P2G_WARPS 4
 #endif
 #ifndef P2G_MIN_CTAS
-#define P2G_MIN_CTAS 5
+#define P2G_MIN_CTAS 4
 #endif
 #define P2G_REC_STRIDE 33  // float4 per record slot: 32 lanes + 1 pad (bank-conflict-free phase B reads)
 #define P2G_REC_SLOTS 12   // 9 x {Y_ij.xyz, wx_i wy_j} + 3 x {R_k.xyz, wz_k}
 
+#define P2G_NSTAGE 6       // xm, vv, c0, c1, cs, s1
+
 struct __align__(16) P2GWarpSmem {
     float4 rec[P2G_REC_SLOTS * P2G_REC_STRIDE];
     float4 tile[MPMK_TILE_NODES];
+    float4 stage[P2G_NSTAGE][32];  // next batch's particle records, in flight (cp.async) while this batch is scattered
 };
 
 struct P2GArgs {
@@ -56,29 +59,51 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int i = lane; i < MPMK_TILE_NODES; i += 32) S.tile[i] = zero4;
     __syncwarp();
-    const uint32_t n_items = a.cnt->n_items;
     const int n = a.n_grid;
 
-    while (true) {
-        uint32_t it = 0;
-        if (lane == 0) it = atomicAdd(&a.cnt->p2g_cursor, 1u);
-        it = __shfl_sync(0xffffffffu, it, 0);
-        if (it >= n_items) break;
-        const uint4 item = a.items[it];
-        const int tz = item.z % a.nt, ty = (item.z / a.nt) % a.nt, tx = item.z / (a.nt * a.nt);
-        int cur_cell = -1;
-        float4 acc = zero4;
+    // Batches stream across dynamically fetched work items through a three-deep pipeline (see g2p.cu):
+    // C = permutation/key loads in flight, B = particle records in flight (cp.async into S.stage, issued as
+    // soon as phase A has pulled batch A's records into registers), A = being scattered.
+    BatchStream bs;
+    bs.init(a.items, &a.cnt->p2g_cursor, a.cnt->n_items);
+    BatchDesc dA = bs.next(lane);
+    if (dA.count == 0) return;
+    uint32_t pA = 0, kA = 0, pB = 0, kB = 0, pC = 0, kC = 0;
+    if (lane < dA.count) { pA = a.perm[dA.base + lane]; kA = a.skeys[dA.base + lane]; }
+    BatchDesc dB = bs.next(lane);
+    if (lane < dB.count) { pB = a.perm[dB.base + lane]; kB = a.skeys[dB.base + lane]; }
+    if (lane < dA.count) {
+        cp_async16(&S.stage[0][lane], a.xm + pA); cp_async16(&S.stage[1][lane], a.vv + pA);
+        cp_async16(&S.stage[2][lane], a.c0 + pA); cp_async16(&S.stage[3][lane], a.c1 + pA);
+        cp_async16(&S.stage[4][lane], a.cs + pA); cp_async16(&S.stage[5][lane], a.s1 + pA);
+    }
+    cp_async_commit();
+    int cur_cell = -1;
+    float4 acc = zero4;
+    int tx = 0, ty = 0, tz = 0;
 
-        for (uint32_t b0 = 0; b0 < item.y; b0 += 32) {
-            const int nbatch = min(32u, item.y - b0);
+    while (dA.count > 0) {
+        if (dA.first) { tz = dA.tile % a.nt; ty = (dA.tile / a.nt) % a.nt; tx = dA.tile / (a.nt * a.nt); }
+        const int nbatch = dA.count;
             int my_cell = 64;  // lanes past the end of the batch never match a real cell
+            cp_async_wait<0>();
+            float4 X = zero4, V = zero4, C0 = zero4, C1 = zero4, CS = zero4, S1 = zero4;
+            if (lane < nbatch) {
+                X = S.stage[0][lane]; V = S.stage[1][lane]; C0 = S.stage[2][lane];
+                C1 = S.stage[3][lane]; CS = S.stage[4][lane]; S1 = S.stage[5][lane];
+            }
+            // the stage slots are free again: start batch B's records, then batch C's permutation entries
+            if (lane < dB.count) {
+                cp_async16(&S.stage[0][lane], a.xm + pB); cp_async16(&S.stage[1][lane], a.vv + pB);
+                cp_async16(&S.stage[2][lane], a.c0 + pB); cp_async16(&S.stage[3][lane], a.c1 + pB);
+                cp_async16(&S.stage[4][lane], a.cs + pB); cp_async16(&S.stage[5][lane], a.s1 + pB);
+            }
+            cp_async_commit();
+            const BatchDesc dC = bs.next(lane);
+            if (lane < dC.count) { pC = a.perm[dC.base + lane]; kC = a.skeys[dC.base + lane]; }
             // ---------------- phase A: lane = particle ----------------
             if (lane < nbatch) {
-                const uint32_t r = item.x + b0 + lane;
-                const uint32_t p = a.perm[r];
-                const uint32_t key = a.skeys[r];
-                const float4 X = ldg4(a.xm + p), V = ldg4(a.vv + p), C0 = ldg4(a.c0 + p), C1 = ldg4(a.c1 + p),
-                             CS = ldg4(a.cs + p), S1 = ldg4(a.s1 + p);
+                const uint32_t key = kA;
                 my_cell = key & 63;
                 const int lx = my_cell >> 4, ly = (my_cell >> 2) & 3, lz = my_cell & 3;
                 const float m = X.w, vol = S1.w;
@@ -188,25 +213,29 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
                 }
             }
             __syncwarp();
-        }
-        // last cell run -> tile
-        if (cur_cell >= 0 && node_lane) {
-            const int nd = (cur_cell >> 4) * 36 + ((cur_cell >> 2) & 3) * 6 + (cur_cell & 3) + noff;
-            float4 t = S.tile[nd];
-            t.x += acc.x; t.y += acc.y; t.z += acc.z; t.w += acc.w;
-            S.tile[nd] = t;
-        }
-        __syncwarp();
-        // tile -> global grid (16-byte vector reductions), and reset for the next item
-        for (int i = lane; i < MPMK_TILE_NODES; i += 32) {
-            const float4 t = S.tile[i];
-            S.tile[i] = zero4;
-            if (t.x != 0.f || t.y != 0.f || t.z != 0.f || t.w != 0.f) {
-                const int gx = 4 * tx + i / 36, gy = 4 * ty + (i / 6) % 6, gz = 4 * tz + i % 6;
-                if (gx < n && gy < n && gz < n) red_add_v4(a.grid_in + (((size_t)gx * n + gy) * n + gz), t);
+            // end of the item: last cell run -> tile, tile -> global grid (16-byte vector reductions)
+            if (dB.count == 0 || dB.first) {
+                if (cur_cell >= 0 && node_lane) {
+                    const int nd = (cur_cell >> 4) * 36 + ((cur_cell >> 2) & 3) * 6 + (cur_cell & 3) + noff;
+                    float4 t = S.tile[nd];
+                    t.x += acc.x; t.y += acc.y; t.z += acc.z; t.w += acc.w;
+                    S.tile[nd] = t;
+                }
+                __syncwarp();
+                for (int i = lane; i < MPMK_TILE_NODES; i += 32) {
+                    const float4 t = S.tile[i];
+                    S.tile[i] = zero4;
+                    if (t.x != 0.f || t.y != 0.f || t.z != 0.f || t.w != 0.f) {
+                        const int gx = 4 * tx + i / 36, gy = 4 * ty + (i / 6) % 6, gz = 4 * tz + i % 6;
+                        if (gx < n && gy < n && gz < n) red_add_v4(a.grid_in + (((size_t)gx * n + gy) * n + gz), t);
+                    }
+                }
+                cur_cell = -1;
+                acc = zero4;
+                __syncwarp();
             }
-        }
-        __syncwarp();
+            dA = dB; pA = pB; kA = kB;
+            dB = dC; pB = pC; kB = kC;
     }
 }
 
