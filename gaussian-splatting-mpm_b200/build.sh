@@ -3,7 +3,8 @@
 set -euo pipefail
 cd "$(dirname "$0")"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
-FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -Xcompiler -fvisibility=hidden"
+NCCL_INC=$(ls -d "$(python -c 'import sysconfig;print(sysconfig.get_paths()["purelib"])')"/nvidia/nccl/include 2>/dev/null || echo /usr/include)
+FLAGS="-I$NCCL_INC -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -Xcompiler -fvisibility=hidden"
 OUT=${OUT:-lib/libmpmk.so}
 BUILD=${BUILD:-build}
 mkdir -p "$BUILD" "$(dirname "$OUT")"
@@ -16,5 +17,5 @@ for f in csrc/*.cu; do
   fi
 done
 for p in "${pids[@]:-}"; do [ -n "$p" ] && wait "$p"; done
-$NVCC -shared -gencode arch=compute_100a,code=sm_100a -o "$OUT" "$BUILD"/*.o
+$NVCC -shared -gencode arch=compute_100a,code=sm_100a -o "$OUT" "$BUILD"/*.o -ldl
 echo "built $OUT"

@@ -65,6 +65,7 @@ extern "C" int mpmk_create(mpmk_ctx** out, int device, int n_grid, double grid_e
 
 extern "C" int mpmk_destroy(mpmk_ctx* ctx) {
     if (!ctx) return 0;
+    mpmk_mg_finalize(ctx);
     for (int i = 0; i < ctx->n_graphs; ++i) cudaGraphExecDestroy(ctx->graphs[i].exec);
     cudaFree(ctx->keys_alt); cudaFree(ctx->sorted_keys); cudaFree(ctx->perm); cudaFree(ctx->perm_alt);
     cudaFree(ctx->hist); cudaFree(ctx->hist_tot); cudaFree(ctx->items); cudaFree(ctx->block_stamp);
@@ -162,6 +163,7 @@ static int substep_impl(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cu
     if ((rc = mpmk_launch_sort(ctx, s))) return rc;
     if ((rc = mpmk_launch_prepare(ctx, s))) return rc;
     if ((rc = mpmk_launch_p2g(ctx, dt, ops, s))) return rc;
+    if ((rc = mpmk_mg_halo_sum(ctx, s))) return rc;  // no-op unless a slab is set (mg.cu)
     if ((rc = mpmk_launch_grid(ctx, dt, ops, s))) return rc;
     return mpmk_launch_g2p(ctx, dt, s);
 }
@@ -181,6 +183,17 @@ extern "C" int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* op
     memset(&zero_ops, 0, sizeof(zero_ops));
     if (!ops) ops = &zero_ops;
     const uint32_t user_flags = ctx->prm.flags;
+    if (ctx->mg.enabled) {
+        // slab mode: the substeps carry ncclSend/ncclRecv; they are issued eagerly on the caller's stream
+        // (no host synchronisation in between), not captured
+        int rc = 0;
+        for (int i = 0; i < n_steps && rc == 0; ++i) {
+            ctx->prm.flags = (i == n_steps - 1) ? user_flags : (user_flags & ~MPMK_WRITE_FTRIAL);
+            rc = substep_impl(ctx, dt, ops, s);
+        }
+        ctx->prm.flags = user_flags;
+        return rc;
+    }
     // look for a captured graph with identical launch parameters
     for (int i = 0; i < ctx->n_graphs; ++i) {
         mpmk_ctx::GraphEntry& g = ctx->graphs[i];

@@ -10,7 +10,9 @@
 
 #define MPMK_TILE 4                 // cells per tile edge; a tile's stencil covers 6^3 nodes
 #define MPMK_TILE_NODES 216         // 6*6*6
-#define MPMK_ITEM_MAX 512           // particles per p2g/g2p work item (tile chunk)
+#ifndef MPMK_ITEM_MAX
+#define MPMK_ITEM_MAX 256           // particles per p2g/g2p work item (tile chunk)
+#endif
 #define MPMK_SORT_CTA 256           // threads per sort CTA
 #define MPMK_SORT_ROUNDS 16         // keys per thread per sort CTA
 #define MPMK_SORT_CHUNK (MPMK_SORT_CTA * MPMK_SORT_ROUNDS)
@@ -24,6 +26,18 @@ struct DevCounters {
     uint32_t p2g_cursor;   // dynamic work fetch
     uint32_t g2p_cursor;
     uint32_t pad[2];
+};
+
+// multi-GPU slab state (mg.cu)
+struct MgState {
+    void* comm;   // ncclComm_t
+    int rank, world;
+    bool enabled;
+    int x_lo, x_hi, ghost;
+    int y_lo, y_hi;          // row range the exchange / dense passes are restricted to
+    int lo0, lo1, hi0, hi1;  // shared plane ranges with rank-1 / rank+1 (empty when lo1 == lo0)
+    void* recv_lo;
+    void* recv_hi;
 };
 
 struct mpmk_ctx {
@@ -74,6 +88,7 @@ struct mpmk_ctx {
     } graphs[4];
     int n_graphs;
     cudaStream_t cap_stream;  // graphs are captured here (the legacy default stream cannot be captured)
+    MgState mg;
     char err[512];
 };
 
@@ -131,6 +146,10 @@ __device__ __forceinline__ void cp_async16(void* smem, const void* gptr) {
     const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gptr) : "memory");
 }
+__device__ __forceinline__ void cp_async4(void* smem, const void* gptr) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(gptr) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
@@ -142,18 +161,15 @@ struct BatchDesc {
     bool first;     // first batch of its item
 };
 
-// warp-uniform stream of batches over dynamically fetched work items
+// Warp-uniform stream of batches over dynamically fetched work items (one atomic on the cursor per item).
+// Requesting the next item ahead of time was tried and measured slower: a warp that reserves an item
+// early lengthens the tail of the persistent grid (items are coarse, ~3.5 per warp at 4 M particles).
 struct BatchStream {
-    const uint4* items;
-    uint32_t* cursor;
-    uint32_t n_items;
-    uint4 item;
+    uint4 item;  // current item {begin, count, tile, -}
     uint32_t off;
     bool done;
-    __device__ __forceinline__ void init(const uint4* it, uint32_t* cur, uint32_t n) {
-        items = it; cursor = cur; n_items = n; item = make_uint4(0u, 0u, 0u, 0u); off = 0; done = false;
-    }
-    __device__ __forceinline__ BatchDesc next(int lane) {
+    __device__ __forceinline__ void init() { item = make_uint4(0u, 0u, 0u, 0u); off = 0; done = false; }
+    __device__ __forceinline__ BatchDesc next(int lane, const uint4* __restrict__ items, uint32_t* cursor, uint32_t n_items) {
         BatchDesc d;
         d.base = 0; d.tile = 0; d.count = 0; d.first = false;
         if (done) return d;
@@ -183,3 +199,6 @@ int mpmk_launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaS
 int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s);
 int mpmk_p2g_init(mpmk_ctx* ctx);
 int mpmk_g2p_init(mpmk_ctx* ctx);
+int mpmk_mg_clear_shared(mpmk_ctx* ctx, cudaStream_t s);
+int mpmk_mg_halo_sum(mpmk_ctx* ctx, cudaStream_t s);
+extern "C" int mpmk_mg_finalize(mpmk_ctx* ctx);

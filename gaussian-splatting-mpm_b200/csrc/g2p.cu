@@ -31,6 +31,11 @@ struct G2PArgs {
     ConstParams cp;
 };
 
+__device__ __forceinline__ void bspline_w(float f, float* w) {
+    float wa = 1.5f - f, wb = f - 1.0f, wc = f - 0.5f;
+    w[0] = wa * wa * 0.5f; w[1] = 0.75f - wb * wb; w[2] = wc * wc * 0.5f;
+}
+
 __device__ __forceinline__ void bspline(float f, float* w, float* dw) {
     float wa = 1.5f - f, wb = f - 1.0f, wc = f - 0.5f;
     w[0] = wa * wa * 0.5f; w[1] = 0.75f - wb * wb; w[2] = wc * wc * 0.5f;
@@ -57,6 +62,8 @@ __device__ __forceinline__ void bspline(float f, float* w, float* dw) {
 struct __align__(16) G2PWarpSmem {
     float4 rec[2][G2P_NREC][32];
     float4 tile[MPMK_TILE_NODES];
+    uint32_t perm[2][32];  // permutation entries of batches B/C (ring), kept out of registers
+    uint32_t key[3][32];   // keys of batches A/B/C (ring)
 };
 
 __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PArgs a) {
@@ -69,24 +76,35 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
     const float k4 = 4.0f * a.inv_dx;
 
     BatchStream bs;
-    bs.init(a.items, &a.cnt->g2p_cursor, a.cnt->n_items);
-    BatchDesc dA = bs.next(lane);
+    bs.init();
+    const uint32_t n_items = a.cnt->n_items;
+    BatchDesc dA = bs.next(lane, a.items, &a.cnt->g2p_cursor, n_items);
     if (dA.count == 0) return;
-    uint32_t pA = 0, kA = 0, pB = 0, kB = 0, pC = 0, kC = 0;
-    if (lane < dA.count) { pA = a.perm[dA.base + lane]; kA = a.skeys[dA.base + lane]; }
-    BatchDesc dB = bs.next(lane);
-    if (lane < dB.count) { pB = a.perm[dB.base + lane]; kB = a.skeys[dB.base + lane]; }
-    int stage = 0;
+    // prologue: batch A's permutation entries synchronously, its records and batch B's entries async
+    int stage = 0;   // record stage holding batch A
+    int kslot = 0;   // key ring slot of batch A (B = +1, C = +2 mod 3)
+    int pslot = 0;   // perm ring slot of batch B (C = the other)
+    uint32_t pA = 0;
     if (lane < dA.count) {
+        pA = a.perm[dA.base + lane];
+        S.key[0][lane] = a.skeys[dA.base + lane];
         cp_async16(&S.rec[0][0][lane], a.xm + pA);
         cp_async16(&S.rec[0][1][lane], a.f0 + pA);
         cp_async16(&S.rec[0][2][lane], a.f1 + pA);
         cp_async16(&S.rec[0][3][lane], a.f2 + pA);
         cp_async16(&S.rec[0][4][lane], a.meta + pA);
     }
+    BatchDesc dB = bs.next(lane, a.items, &a.cnt->g2p_cursor, n_items);
+    if (lane < dB.count) {
+        cp_async4(&S.perm[0][lane], a.perm + dB.base + lane);
+        cp_async4(&S.key[1][lane], a.skeys + dB.base + lane);
+    }
     cp_async_commit();
 
     while (dA.count > 0) {
+        // batch A's records and batch B's permutation entries (issued one iteration ago) have landed
+        cp_async_wait<0>();
+        __syncwarp();
         const int tz = dA.tile % a.nt, ty = (dA.tile / a.nt) % a.nt, tx = dA.tile / (a.nt * a.nt);
         if (dA.first) {
             // a new item: restage the node tile (the previous item's gathers ended with __syncwarp)
@@ -97,38 +115,47 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
             }
         }
         cp_async_commit();
+        uint32_t pB = 0;
         if (lane < dB.count) {
+            pB = S.perm[pslot][lane];
             cp_async16(&S.rec[stage ^ 1][0][lane], a.xm + pB);
             cp_async16(&S.rec[stage ^ 1][1][lane], a.f0 + pB);
             cp_async16(&S.rec[stage ^ 1][2][lane], a.f1 + pB);
             cp_async16(&S.rec[stage ^ 1][3][lane], a.f2 + pB);
             cp_async16(&S.rec[stage ^ 1][4][lane], a.meta + pB);
         }
+        const BatchDesc dC = bs.next(lane, a.items, &a.cnt->g2p_cursor, n_items);
+        const int kslotC = (kslot + 2) % 3;
+        if (lane < dC.count) {
+            cp_async4(&S.perm[pslot ^ 1][lane], a.perm + dC.base + lane);
+            cp_async4(&S.key[kslotC][lane], a.skeys + dC.base + lane);
+        }
         cp_async_commit();
-        const BatchDesc dC = bs.next(lane);
-        if (lane < dC.count) { pC = a.perm[dC.base + lane]; kC = a.skeys[dC.base + lane]; }
-        cp_async_wait<1>();  // batch A's records and the tile have landed; batch B's may still be in flight
+        cp_async_wait<1>();  // the tile has landed; batch B's records / batch C's entries stay in flight
         __syncwarp();
 
         if (lane < dA.count) {
             const uint32_t r = dA.base + lane;
-            const uint32_t key = kA;
+            const uint32_t key = S.key[kslot][lane];
             const float4 X = S.rec[stage][0][lane];
             const int lx = (key >> 4) & 3, ly = (key >> 2) & 3, lz = key & 3;
             const float fx = __fmul_rn(X.x, a.inv_dx) - (float)(4 * tx + lx);
             const float fy = __fmul_rn(X.y, a.inv_dx) - (float)(4 * ty + ly);
             const float fz = __fmul_rn(X.z, a.inv_dx) - (float)(4 * tz + lz);
-            float wx[3], wy[3], wz[3], dwx[3], dwy[3], dwz[3];
-            bspline(fx, wx, dwx); bspline(fy, wy, dwy); bspline(fz, wz, dwz);
-            // w_d (off_d - f_d): the APIC moment weights, shifted per axis so no large terms cancel
-            const float wxd[3] = {wx[0] * (0.f - fx), wx[1] * (1.f - fx), wx[2] * (2.f - fx)};
-            const float wyd[3] = {wy[0] * (0.f - fy), wy[1] * (1.f - fy), wy[2] * (2.f - fy)};
+            // only w is kept live; dw (linear in f) and the APIC moment weights w_d (off_d - f_d), shifted per
+            // axis so no large terms cancel, are re-derived where they are used (register pressure)
+            float wx[3], wy[3], wz[3], dwz[3];
+            bspline_w(fx, wx); bspline_w(fy, wy); bspline_w(fz, wz);
+            dwz[0] = fz - 1.5f; dwz[1] = -2.0f * (fz - 1.0f); dwz[2] = fz - 0.5f;
             const float wzd[3] = {wz[0] * (0.f - fz), wz[1] * (1.f - fz), wz[2] * (2.f - fz)};
 
             // sums over the stencil: v, M_d = sum w (off_d - f_d) v (d=x,y,z), G_d = sum (dw_d-weighted) v
             float v[3] = {0, 0, 0}, Mx[3] = {0, 0, 0}, My[3] = {0, 0, 0}, Mz[3] = {0, 0, 0};
             float Gx[3] = {0, 0, 0}, Gy[3] = {0, 0, 0}, Gz[3] = {0, 0, 0};
             const float4* g = S.tile + (lx * 36 + ly * 6 + lz);
+#ifdef EXP_NOGATHER
+            { const float4 g0 = g[0]; v[0] = g0.x; v[1] = g0.y; v[2] = g0.z; Mx[0] = fx; My[1] = fy; Mz[2] = fz; Gx[0] = wx[0]; Gy[1] = wy[1]; Gz[2] = wz[2] + wzd[0] + dwz[1]; }
+#else
 #pragma unroll
             for (int i = 0; i < 3; ++i) {
                 float A[3] = {0, 0, 0}, Ay[3] = {0, 0, 0}, Gyi[3] = {0, 0, 0}, Az[3] = {0, 0, 0}, Gzi[3] = {0, 0, 0};
@@ -147,7 +174,8 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
                     const float dy_ = dwz[0] * g0.y + dwz[1] * g1.y + dwz[2] * g2.y;
                     const float dz_ = dwz[0] * g0.z + dwz[1] * g1.z + dwz[2] * g2.z;
                     // contraction along y
-                    const float wj = wy[j], wjj = wyd[j], dj = dwy[j];
+                    const float wj = wy[j], wjj = wy[j] * ((float)j - fy);
+                    const float dj = (j == 0) ? fy - 1.5f : (j == 1) ? -2.0f * (fy - 1.0f) : fy - 0.5f;
                     A[0] += wj * ax; A[1] += wj * ay; A[2] += wj * az;
                     Ay[0] += wjj * ax; Ay[1] += wjj * ay; Ay[2] += wjj * az;
                     Gyi[0] += dj * ax; Gyi[1] += dj * ay; Gyi[2] += dj * az;
@@ -155,7 +183,8 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
                     Gzi[0] += wj * dx_; Gzi[1] += wj * dy_; Gzi[2] += wj * dz_;
                 }
                 // contraction along x
-                const float wi = wx[i], wii = wxd[i], di = dwx[i];
+                const float wi = wx[i], wii = wx[i] * ((float)i - fx);
+                const float di = (i == 0) ? fx - 1.5f : (i == 1) ? -2.0f * (fx - 1.0f) : fx - 0.5f;
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
                     v[c] += wi * A[c];
@@ -167,6 +196,7 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
                     Gz[c] += wi * Gzi[c];
                 }
             }
+#endif
             // utils.py:266-275: v, x, C = sum w v (x) (off - f) * 4 inv_dx
             const float nx = X.x + dt * v[0], ny = X.y + dt * v[1], nz = X.z + dt * v[2];
             a.oxm[r] = make_float4(nx, ny, nz, X.w);
@@ -234,9 +264,11 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
             a.of2[r] = make_float4(Fn[8], mu, lam, ys);
         }
         __syncwarp();  // all lanes are done with the tile and this stage before either is overwritten
-        dA = dB; pA = pB; kA = kB;
-        dB = dC; pB = pC; kB = kC;
+        dA = dB; pA = pB;
+        dB = dC;
         stage ^= 1;
+        pslot ^= 1;
+        kslot = (kslot + 1) % 3;
     }
     cp_async_wait<0>();
 }

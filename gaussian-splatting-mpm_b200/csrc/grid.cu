@@ -10,6 +10,48 @@ struct GridOpsArg {
     mpmk_grid_op ops[MPMK_MAX_GRID_OPS];
 };
 
+__device__ __forceinline__ void grid_node_update(const float4* __restrict__ gin, float4* __restrict__ gout, int ix, int iy,
+                                                 int iz, int n, float dx, float dt, float gx, float gy, float gz,
+                                                 const GridOpsArg& ops) {
+    size_t node = ((size_t)ix * n + iy) * n + iz;
+    float4 m = gin[node];
+    float vx = 0.f, vy = 0.f, vz = 0.f;
+    if (m.w > 1e-15f) {
+        vx = __fdiv_rn(m.x, m.w) + dt * gx;
+        vy = __fdiv_rn(m.y, m.w) + dt * gy;
+        vz = __fdiv_rn(m.z, m.w) + dt * gz;
+    }
+    // geometric predicates are discontinuous: keep every product and difference individually rounded
+    // (no FMA contraction) so a node lying exactly on a box face / collider plane falls on the same
+    // side as in the reference arithmetic (float(idx) * dx - c)
+    const float px = __fmul_rn((float)ix, dx), py = __fmul_rn((float)iy, dx), pz = __fmul_rn((float)iz, dx);
+    for (int o = 0; o < ops.n_ops; ++o) {
+        const mpmk_grid_op& op = ops.ops[o];
+        if (op.type == MPMK_OP_FIXED_CUBE) {
+            if (fabsf(__fsub_rn(px, op.a[0])) < op.b[0] && fabsf(__fsub_rn(py, op.a[1])) < op.b[1] &&
+                fabsf(__fsub_rn(pz, op.a[2])) < op.b[2]) {
+                vx = 0.f; vy = 0.f; vz = 0.f;
+            }
+        } else {
+            const float ox = __fsub_rn(px, op.a[0]), oy = __fsub_rn(py, op.a[1]), oz = __fsub_rn(pz, op.a[2]);
+            const float nx = op.b[0], ny = op.b[1], nz = op.b[2];
+            const float dp = __fadd_rn(__fadd_rn(__fmul_rn(ox, nx), __fmul_rn(oy, ny)), __fmul_rn(oz, nz));
+            if (dp < 0.f) {
+                float nc = vx * nx + vy * ny + vz * nz;
+                float mn = fminf(nc, 0.f);
+                vx -= mn * nx; vy -= mn * ny; vz -= mn * nz;
+                float len = sqrtf(vx * vx + vy * vy + vz * vz);
+                if (nc < 0.f && len > 1e-20f) {
+                    float sc = fmaxf(0.f, len + nc * op.c);
+                    vx = sc * __fdiv_rn(vx, len); vy = sc * __fdiv_rn(vy, len); vz = sc * __fdiv_rn(vz, len);
+                }
+                vx *= 0.99f; vy *= 0.99f; vz *= 0.99f;  // collider.py:44, every node below the plane (Q4)
+            }
+        }
+    }
+    gout[node] = make_float4(vx, vy, vz, 0.f);
+}
+
 __global__ void __launch_bounds__(256) k_grid(const float4* __restrict__ gin, float4* __restrict__ gout,
                                               const uint32_t* __restrict__ list, const uint32_t* __restrict__ count,
                                               int n, int nb, float dx, float dt, float gx, float gy, float gz,
@@ -21,43 +63,20 @@ __global__ void __launch_bounds__(256) k_grid(const float4* __restrict__ gin, fl
         int bz = b % nb, by = (b / nb) % nb, bx = b / (nb * nb);
         int ix = 4 * bx + (l >> 4), iy = 4 * by + ((l >> 2) & 3), iz = 4 * bz + (l & 3);
         if (ix >= n || iy >= n || iz >= n) continue;
-        size_t node = ((size_t)ix * n + iy) * n + iz;
-        float4 m = gin[node];
-        float vx = 0.f, vy = 0.f, vz = 0.f;
-        if (m.w > 1e-15f) {
-            vx = __fdiv_rn(m.x, m.w) + dt * gx;
-            vy = __fdiv_rn(m.y, m.w) + dt * gy;
-            vz = __fdiv_rn(m.z, m.w) + dt * gz;
-        }
-        // geometric predicates are discontinuous: keep every product and difference individually rounded
-        // (no FMA contraction) so a node lying exactly on a box face / collider plane falls on the same
-        // side as in the reference arithmetic (float(idx) * dx - c)
-        const float px = __fmul_rn((float)ix, dx), py = __fmul_rn((float)iy, dx), pz = __fmul_rn((float)iz, dx);
-        for (int o = 0; o < ops.n_ops; ++o) {
-            const mpmk_grid_op& op = ops.ops[o];
-            if (op.type == MPMK_OP_FIXED_CUBE) {
-                if (fabsf(__fsub_rn(px, op.a[0])) < op.b[0] && fabsf(__fsub_rn(py, op.a[1])) < op.b[1] &&
-                    fabsf(__fsub_rn(pz, op.a[2])) < op.b[2]) {
-                    vx = 0.f; vy = 0.f; vz = 0.f;
-                }
-            } else {
-                const float ox = __fsub_rn(px, op.a[0]), oy = __fsub_rn(py, op.a[1]), oz = __fsub_rn(pz, op.a[2]);
-                const float nx = op.b[0], ny = op.b[1], nz = op.b[2];
-                const float dp = __fadd_rn(__fadd_rn(__fmul_rn(ox, nx), __fmul_rn(oy, ny)), __fmul_rn(oz, nz));
-                if (dp < 0.f) {
-                    float nc = vx * nx + vy * ny + vz * nz;
-                    float mn = fminf(nc, 0.f);
-                    vx -= mn * nx; vy -= mn * ny; vz -= mn * nz;
-                    float len = sqrtf(vx * vx + vy * vy + vz * vz);
-                    if (nc < 0.f && len > 1e-20f) {
-                        float sc = fmaxf(0.f, len + nc * op.c);
-                        vx = sc * __fdiv_rn(vx, len); vy = sc * __fdiv_rn(vy, len); vz = sc * __fdiv_rn(vz, len);
-                    }
-                    vx *= 0.99f; vy *= 0.99f; vz *= 0.99f;  // collider.py:44, every node below the plane (Q4)
-                }
-            }
-        }
-        gout[node] = make_float4(vx, vy, vz, 0.f);
+        grid_node_update(gin, gout, ix, iy, iz, n, dx, dt, gx, gy, gz, ops);
+    }
+}
+
+// multi-GPU: the same update, densely over the planes [x0, x1) shared with a neighbouring slab (mg.cu)
+__global__ void __launch_bounds__(256) k_grid_planes(const float4* __restrict__ gin, float4* __restrict__ gout, int x0, int x1,
+                                                     int y0, int y1, int n, float dx, float dt, float gx, float gy, float gz,
+                                                     const GridOpsArg ops) {
+    const int64_t per_plane = (int64_t)(y1 - y0) * n, total = per_plane * (x1 - x0);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int ix = x0 + (int)(i / per_plane);
+        const int64_t rem = i % per_plane;
+        const int iy = y0 + (int)(rem / n), iz = (int)(rem % n);
+        grid_node_update(gin, gout, ix, iy, iz, n, dx, dt, gx, gy, gz, ops);
     }
 }
 
@@ -75,5 +94,16 @@ int mpmk_launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaS
                                              ctx->n_grid, ctx->nb, ctx->dx, dt, ctx->prm.gravity[0], ctx->prm.gravity[1],
                                              ctx->prm.gravity[2], a);
     MPMK_LAUNCH_CHECK(ctx);
+    if (ctx->mg.enabled) {
+        const MgState& m = ctx->mg;
+        const int r0[2] = {m.lo0, m.hi0}, r1[2] = {m.lo1, m.hi1};
+        for (int k = 0; k < 2; ++k) {
+            if (r1[k] <= r0[k]) continue;
+            k_grid_planes<<<ctx->sm_count * 4, 256, 0, s>>>((const float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out, r0[k], r1[k],
+                                                            m.y_lo, m.y_hi, ctx->n_grid, ctx->dx, dt, ctx->prm.gravity[0], ctx->prm.gravity[1],
+                                                            ctx->prm.gravity[2], a);
+            MPMK_LAUNCH_CHECK(ctx);
+        }
+    }
     return 0;
 }

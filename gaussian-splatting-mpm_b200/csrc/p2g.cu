@@ -65,12 +65,13 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
     // C = permutation/key loads in flight, B = particle records in flight (cp.async into S.stage, issued as
     // soon as phase A has pulled batch A's records into registers), A = being scattered.
     BatchStream bs;
-    bs.init(a.items, &a.cnt->p2g_cursor, a.cnt->n_items);
-    BatchDesc dA = bs.next(lane);
+    bs.init();
+    const uint32_t n_items = a.cnt->n_items;
+    BatchDesc dA = bs.next(lane, a.items, &a.cnt->p2g_cursor, n_items);
     if (dA.count == 0) return;
     uint32_t pA = 0, kA = 0, pB = 0, kB = 0, pC = 0, kC = 0;
     if (lane < dA.count) { pA = a.perm[dA.base + lane]; kA = a.skeys[dA.base + lane]; }
-    BatchDesc dB = bs.next(lane);
+    BatchDesc dB = bs.next(lane, a.items, &a.cnt->p2g_cursor, n_items);
     if (lane < dB.count) { pB = a.perm[dB.base + lane]; kB = a.skeys[dB.base + lane]; }
     if (lane < dA.count) {
         cp_async16(&S.stage[0][lane], a.xm + pA); cp_async16(&S.stage[1][lane], a.vv + pA);
@@ -99,7 +100,7 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
                 cp_async16(&S.stage[4][lane], a.cs + pB); cp_async16(&S.stage[5][lane], a.s1 + pB);
             }
             cp_async_commit();
-            const BatchDesc dC = bs.next(lane);
+            const BatchDesc dC = bs.next(lane, a.items, &a.cnt->p2g_cursor, n_items);
             if (lane < dC.count) { pC = a.perm[dC.base + lane]; kC = a.skeys[dC.base + lane]; }
             // ---------------- phase A: lane = particle ----------------
             if (lane < nbatch) {

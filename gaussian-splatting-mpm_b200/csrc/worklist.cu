@@ -66,6 +66,7 @@ int mpmk_launch_prepare(mpmk_ctx* ctx, cudaStream_t s) {
                                                      ctx->block_list[prev], ctx->block_count[prev], ctx->n_grid, ctx->nb,
                                                      ctx->dev_stamp);
     MPMK_LAUNCH_CHECK(ctx);
+    if (ctx->mg.enabled) { int rc = mpmk_mg_clear_shared(ctx, s); if (rc) return rc; }
     MPMK_CHECK(ctx, cudaMemsetAsync(ctx->counters, 0, sizeof(DevCounters), s));
     MPMK_CHECK(ctx, cudaMemsetAsync(ctx->block_count[next], 0, sizeof(uint32_t), s));
     if (ctx->n > 0) {

@@ -185,6 +185,29 @@ MPMK_API int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops,
 MPMK_API int mpmk_export(mpmk_ctx* ctx, const void* init_cov_dev, void* xyz_out_dev /* float[n][3] */,
                 void* cov_out_dev /* float[n][6] */, void* R_out_dev /* float[n][9] */, void* stream);
 
+/* ---- multi-GPU slab decomposition (csrc/mg.cu) ------------------------------
+ * The reference is single-GPU (one ti.init(arch=ti.cuda), dense global fields:
+ * main.py:28, model.py:118-121); these entry points have no counterpart there.
+ * One process per GPU.  Rank r owns the base-cell planes [x_lo, x_hi) of the
+ * grid's slowest axis; between migrations its particles may sit up to `ghost`
+ * cells outside.  After p2g the partial sums on the planes shared with each
+ * neighbour are exchanged (ncclSend/ncclRecv on the caller's stream) and added
+ * symmetrically, after which both neighbours run the grid update on them.
+ * Particle migration is host-orchestrated (harness/slabs.py) between batches.  */
+/* rank 0: create the 128-byte NCCL unique id that the host layer broadcasts     */
+MPMK_API int mpmk_mg_unique_id(const char* nccl_lib_path, void* id_out, int id_bytes);
+/* all ranks: join the communicator (nccl_lib_path: the libnccl.so.2 torch loaded) */
+MPMK_API int mpmk_mg_init(mpmk_ctx* ctx, const char* nccl_lib_path, const void* id, int id_bytes, int rank, int world);
+MPMK_API int mpmk_mg_finalize(mpmk_ctx* ctx);
+/* [y_lo, y_hi): rows of each shared plane that can hold particles' stencils until the
+ * next migration (the exchange, dense clear and dense update are restricted to them);
+ * recv_*_dev: float4[(2*ghost+2) * (y_hi-y_lo) * n_grid] scratch each (NULL at the
+ * outer ranks); from here on mpmk_substep/mpmk_substeps include the halo sum      */
+MPMK_API int mpmk_mg_set_slab(mpmk_ctx* ctx, int x_lo, int x_hi, int ghost, int y_lo, int y_hi, void* recv_lo_dev,
+                              void* recv_hi_dev);
+/* the halo sum alone (stagewise use: after mpmk_p2g, before mpmk_grid_update)     */
+MPMK_API int mpmk_mg_halo_exchange(mpmk_ctx* ctx, void* stream);
+
 /* ---- introspection -------------------------------------------------------- */
 /* synchronises `stream` */
 MPMK_API int mpmk_read_counters(mpmk_ctx* ctx, mpmk_counters* out, void* stream);
