@@ -40,6 +40,8 @@ static int create_impl(mpmk_ctx* ctx, int device, int n_grid, double grid_extent
     const size_t ntiles = (size_t)ctx->nt * ctx->nt * ctx->nt;
     ctx->items_cap = (int64_t)(cap / MPMK_ITEM_MAX + (cap < ntiles ? cap : ntiles) + 8);
     ALLOC0(ctx, ctx->items, (size_t)ctx->items_cap * sizeof(uint4));
+    ALLOC0(ctx, ctx->tile_list, ((cap < ntiles ? cap : ntiles) + 8) * sizeof(uint2));
+    ALLOC0(ctx, ctx->tile_end, ntiles * 4);
     const size_t nblocks = (size_t)ctx->nb * ctx->nb * ctx->nb;
     ALLOC0(ctx, ctx->block_stamp, nblocks * 4);
     ALLOC0(ctx, ctx->block_list[0], nblocks * 4);
@@ -68,7 +70,7 @@ extern "C" int mpmk_destroy(mpmk_ctx* ctx) {
     mpmk_mg_finalize(ctx);
     for (int i = 0; i < ctx->n_graphs; ++i) cudaGraphExecDestroy(ctx->graphs[i].exec);
     cudaFree(ctx->keys_alt); cudaFree(ctx->sorted_keys); cudaFree(ctx->perm); cudaFree(ctx->perm_alt);
-    cudaFree(ctx->hist); cudaFree(ctx->hist_tot); cudaFree(ctx->items); cudaFree(ctx->block_stamp);
+    cudaFree(ctx->hist); cudaFree(ctx->hist_tot); cudaFree(ctx->items); cudaFree(ctx->tile_list); cudaFree(ctx->tile_end); cudaFree(ctx->block_stamp);
     cudaFree(ctx->block_list[0]); cudaFree(ctx->block_list[1]); cudaFree(ctx->block_count[0]); cudaFree(ctx->block_count[1]);
     cudaFree(ctx->counters); cudaFree(ctx->dev_stamp);
     if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);

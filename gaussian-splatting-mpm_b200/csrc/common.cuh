@@ -64,6 +64,8 @@ struct mpmk_ctx {
     uint32_t* hist_tot;      // [digits]
     int64_t n_sort_ctas_cap;
     uint4* items;            // {begin, count, tile, 0}
+    uint2* tile_list;        // non-empty tiles of the current sort: {tile, first sorted index}
+    uint32_t* tile_end;      // [nt^3] one past the last sorted index of each non-empty tile
     int64_t items_cap;
     uint32_t* block_stamp;   // [nb^3]
     uint32_t* block_list[2]; // active node blocks: [cur_list] this substep, [1-cur_list] previous

@@ -34,15 +34,20 @@ __global__ void __launch_bounds__(MPMK_SORT_CTA) k_sort_hist(const uint32_t* __r
     __shared__ uint32_t h[D];
     for (int d = threadIdx.x; d < D; d += MPMK_SORT_CTA) h[d] = 0;
     __syncthreads();
-    int64_t chunk = (int64_t)blockIdx.x * MPMK_SORT_CHUNK;
+    const int64_t chunk = (int64_t)blockIdx.x * MPMK_SORT_CHUNK;
     const unsigned lane = threadIdx.x & 31;
-#pragma unroll 4
-    for (int i = threadIdx.x; i < MPMK_SORT_CHUNK; i += MPMK_SORT_CTA) {
-        int64_t idx = chunk + i;
-        bool valid = idx < n;
-        uint32_t d = valid ? ((keys[idx] >> shift) & (D - 1)) : (uint32_t)D;
-        unsigned peers = __match_any_sync(0xffffffffu, d);
-        if (valid && (peers & ((1u << lane) - 1u)) == 0) atomicAdd(&h[d], (uint32_t)__popc(peers));
+    // all of this thread's keys first (independent loads in flight together), then the ranking
+    uint32_t dg[MPMK_SORT_ROUNDS];
+#pragma unroll
+    for (int r = 0; r < MPMK_SORT_ROUNDS; ++r) {
+        const int64_t idx = chunk + r * MPMK_SORT_CTA + threadIdx.x;
+        dg[r] = (idx < n) ? ((keys[idx] >> shift) & (D - 1)) : (uint32_t)D;
+    }
+#pragma unroll
+    for (int r = 0; r < MPMK_SORT_ROUNDS; ++r) {
+        const uint32_t d = dg[r];
+        const unsigned peers = __match_any_sync(0xffffffffu, d);
+        if (d < (uint32_t)D && (peers & ((1u << lane) - 1u)) == 0) atomicAdd(&h[d], (uint32_t)__popc(peers));
     }
     __syncthreads();
     for (int d = threadIdx.x; d < D; d += MPMK_SORT_CTA) hist[(size_t)d * nctas + blockIdx.x] = h[d];
@@ -115,12 +120,23 @@ __global__ void __launch_bounds__(MPMK_SORT_CTA) k_sort_scatter(const uint32_t* 
     const unsigned lt = (1u << lane) - 1u;
     const int64_t start = (int64_t)blockIdx.x * MPMK_SORT_CHUNK + (int64_t)w * (32 * MPMK_SORT_ROUNDS);
     uint32_t key[MPMK_SORT_ROUNDS];
+    uint32_t val[MPMK_SORT_ROUNDS];
     uint32_t off[MPMK_SORT_ROUNDS];
+    // every key and value of this thread is requested before the first use (the ranking below is a
+    // serial chain through shared memory; loads issued inside it would each expose a DRAM latency)
 #pragma unroll
     for (int r = 0; r < MPMK_SORT_ROUNDS; ++r) {
-        int64_t idx = start + r * 32 + lane;
-        bool valid = idx < n;
-        key[r] = valid ? keys_in[idx] : 0xffffffffu;
+        const int64_t idx = start + r * 32 + lane;
+        key[r] = (idx < n) ? keys_in[idx] : 0xffffffffu;
+    }
+#pragma unroll
+    for (int r = 0; r < MPMK_SORT_ROUNDS; ++r) {
+        const int64_t idx = start + r * 32 + lane;
+        val[r] = (vals_in && idx < n) ? vals_in[idx] : (uint32_t)idx;
+    }
+#pragma unroll
+    for (int r = 0; r < MPMK_SORT_ROUNDS; ++r) {
+        const bool valid = start + r * 32 + lane < n;
         uint32_t d = valid ? ((key[r] >> shift) & (D - 1)) : (uint32_t)D;
         unsigned peers = __match_any_sync(0xffffffffu, d);
         uint32_t rank = __popc(peers & lt);
@@ -144,7 +160,7 @@ __global__ void __launch_bounds__(MPMK_SORT_CTA) k_sort_scatter(const uint32_t* 
             uint32_t d = (key[r] >> shift) & (D - 1);
             uint32_t pos = wh[w][d] + off[r];
             keys_out[pos] = key[r];
-            vals_out[pos] = vals_in ? vals_in[idx] : (uint32_t)idx;
+            vals_out[pos] = val[r];
         }
     }
 }

@@ -7,8 +7,15 @@
 #include "common.cuh"
 
 __global__ void k_clear_blocks(float4* __restrict__ gin, float4* __restrict__ gout, const uint32_t* __restrict__ list,
-                               const uint32_t* __restrict__ count, int n, int nb, uint32_t* stamp) {
-    if (blockIdx.x == 0 && threadIdx.x == 0) *stamp += 1u;  // consumed by k_build_items (next launch on the stream)
+                               const uint32_t* __restrict__ count, int n, int nb, uint32_t* stamp, DevCounters* cnt,
+                               uint32_t* next_count) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        *stamp += 1u;  // consumed by k_build_items (a later launch on the stream)
+        // this substep's counters / block list start empty (the previous substep's kernels are done with them)
+        cnt->n_items = 0u; cnt->n_active_blocks = 0u; cnt->n_tiles = 0u; cnt->n_clamped = 0u;
+        cnt->p2g_cursor = 0u; cnt->g2p_cursor = 0u;
+        *next_count = 0u;
+    }
     const int64_t total = (int64_t)(*count) * 64;
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -24,35 +31,45 @@ __global__ void k_clear_blocks(float4* __restrict__ gin, float4* __restrict__ go
     }
 }
 
-__global__ void k_build_items(const uint32_t* __restrict__ skeys, int64_t n, uint4* __restrict__ items,
-                              DevCounters* cnt, uint32_t* __restrict__ stamp_arr, const uint32_t* __restrict__ stamp_ptr,
-                              uint32_t* __restrict__ blist, uint32_t* __restrict__ bcount, int nt, int nb) {
-    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+// pass 1 over the sorted keys: the first particle of every tile run appends {tile, start} to the tile
+// list, the last one records the run's end in the tile-indexed table (no search, no dependent loads)
+__global__ void __launch_bounds__(256) k_tile_runs(const uint32_t* __restrict__ skeys, int64_t n, uint2* __restrict__ tile_list,
+                                                   uint32_t* __restrict__ tile_end, DevCounters* cnt) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n) return;
-    uint32_t tile = skeys[r] >> 6;
-    if (r > 0 && (skeys[r - 1] >> 6) == tile) return;
-    // first index past this tile's run
-    int64_t lo = r + 1, hi = n;
-    while (lo < hi) {
-        int64_t mid = (lo + hi) >> 1;
-        if ((skeys[mid] >> 6) > tile) hi = mid; else lo = mid + 1;
-    }
-    uint32_t np = (uint32_t)(lo - r);
-    uint32_t ni = (np + MPMK_ITEM_MAX - 1) / MPMK_ITEM_MAX;
-    uint32_t base = atomicAdd(&cnt->n_items, ni);
-    atomicAdd(&cnt->n_tiles, 1u);
-    for (uint32_t j = 0; j < ni; ++j) {
-        uint32_t b0 = j * MPMK_ITEM_MAX;
-        items[base + j] = make_uint4((uint32_t)r + b0, min((uint32_t)MPMK_ITEM_MAX, np - b0), tile, 0u);
-    }
-    int tz = tile % nt, ty = (tile / nt) % nt, tx = tile / (nt * nt);
+    const uint32_t tile = skeys[r] >> 6;
+    const uint32_t prev = r > 0 ? (skeys[r - 1] >> 6) : 0xffffffffu;
+    const uint32_t next = r + 1 < n ? (skeys[r + 1] >> 6) : 0xffffffffu;
+    if (tile != prev) tile_list[atomicAdd(&cnt->n_tiles, 1u)] = make_uint2(tile, (uint32_t)r);
+    if (tile != next) tile_end[tile] = (uint32_t)r + 1u;
+}
+
+// pass 2 over the non-empty tiles: work items (chunks of <= MPMK_ITEM_MAX particles) and the node blocks
+// the tile's stencils reach
+__global__ void __launch_bounds__(256) k_build_items(const uint2* __restrict__ tile_list, const uint32_t* __restrict__ tile_end,
+                                                     uint4* __restrict__ items, DevCounters* cnt, uint32_t* __restrict__ stamp_arr,
+                                                     const uint32_t* __restrict__ stamp_ptr, uint32_t* __restrict__ blist,
+                                                     uint32_t* __restrict__ bcount, int nt, int nb) {
+    const uint32_t n_tiles = cnt->n_tiles;
     const uint32_t stamp = *stamp_ptr;
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n_tiles; t += gridDim.x * blockDim.x) {
+        const uint2 tl = tile_list[t];
+        const uint32_t tile = tl.x, r = tl.y;
+        const uint32_t np = tile_end[tile] - r;
+        const uint32_t ni = (np + MPMK_ITEM_MAX - 1) / MPMK_ITEM_MAX;
+        const uint32_t base = atomicAdd(&cnt->n_items, ni);
+        for (uint32_t j = 0; j < ni; ++j) {
+            const uint32_t b0 = j * MPMK_ITEM_MAX;
+            items[base + j] = make_uint4(r + b0, min((uint32_t)MPMK_ITEM_MAX, np - b0), tile, 0u);
+        }
+        const int tz = tile % nt, ty = (tile / nt) % nt, tx = tile / (nt * nt);
 #pragma unroll
-    for (int d = 0; d < 8; ++d) {
-        int bx = tx + (d >> 2), by = ty + ((d >> 1) & 1), bz = tz + (d & 1);
-        if (bx < nb && by < nb && bz < nb) {
-            uint32_t b = (uint32_t)((bx * nb + by) * nb + bz);
-            if (atomicExch(&stamp_arr[b], stamp) != stamp) blist[atomicAdd(bcount, 1u)] = b;
+        for (int d = 0; d < 8; ++d) {
+            const int bx = tx + (d >> 2), by = ty + ((d >> 1) & 1), bz = tz + (d & 1);
+            if (bx < nb && by < nb && bz < nb) {
+                const uint32_t b = (uint32_t)((bx * nb + by) * nb + bz);
+                if (atomicExch(&stamp_arr[b], stamp) != stamp) blist[atomicAdd(bcount, 1u)] = b;
+            }
         }
     }
 }
@@ -61,18 +78,18 @@ int mpmk_launch_prepare(mpmk_ctx* ctx, cudaStream_t s) {
     if (!ctx->sorted_valid) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_prepare_grid: sort first");
     int prev = ctx->cur_list;
     int next = 1 - prev;
-    // clear what the previous substep touched
+    // clear what the previous substep touched; reset the per-substep counters
     k_clear_blocks<<<ctx->sm_count * 8, 256, 0, s>>>((float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out,
                                                      ctx->block_list[prev], ctx->block_count[prev], ctx->n_grid, ctx->nb,
-                                                     ctx->dev_stamp);
+                                                     ctx->dev_stamp, ctx->counters, ctx->block_count[next]);
     MPMK_LAUNCH_CHECK(ctx);
     if (ctx->mg.enabled) { int rc = mpmk_mg_clear_shared(ctx, s); if (rc) return rc; }
-    MPMK_CHECK(ctx, cudaMemsetAsync(ctx->counters, 0, sizeof(DevCounters), s));
-    MPMK_CHECK(ctx, cudaMemsetAsync(ctx->block_count[next], 0, sizeof(uint32_t), s));
     if (ctx->n > 0) {
-        k_build_items<<<div_up(ctx->n, 256), 256, 0, s>>>(ctx->sorted_keys, ctx->n, ctx->items, ctx->counters,
-                                                          ctx->block_stamp, ctx->dev_stamp, ctx->block_list[next],
-                                                          ctx->block_count[next], ctx->nt, ctx->nb);
+        k_tile_runs<<<div_up(ctx->n, 256), 256, 0, s>>>(ctx->sorted_keys, ctx->n, ctx->tile_list, ctx->tile_end, ctx->counters);
+        MPMK_LAUNCH_CHECK(ctx);
+        k_build_items<<<ctx->sm_count, 256, 0, s>>>(ctx->tile_list, ctx->tile_end, ctx->items, ctx->counters, ctx->block_stamp,
+                                                    ctx->dev_stamp, ctx->block_list[next], ctx->block_count[next], ctx->nt,
+                                                    ctx->nb);
         MPMK_LAUNCH_CHECK(ctx);
     }
     ctx->cur_list = next;
