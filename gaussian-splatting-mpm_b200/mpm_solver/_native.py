@@ -57,6 +57,24 @@ class MpmkError(RuntimeError):
     pass
 
 
+NCCL_ID_BYTES = 128
+
+
+def nccl_library_path():
+    """Path of the libnccl.so.2 this process's torch uses (the data path dlopens the same library)."""
+    try:
+        with open("/proc/self/maps") as f:
+            for line in f:
+                if "libnccl.so" in line:
+                    return line.split()[-1]
+    except OSError:
+        pass
+    import glob
+    import sysconfig
+    hits = glob.glob(os.path.join(sysconfig.get_paths()["purelib"], "nvidia", "nccl", "lib", "libnccl.so*"))
+    return hits[0] if hits else "libnccl.so.2"
+
+
 _lib = None
 
 
@@ -95,7 +113,13 @@ def lib():
         "mpmk_export": (i, [vp, vp, vp, vp, vp, vp]),
         "mpmk_read_counters": (i, [vp, C.POINTER(Counters), vp]),
         "mpmk_launch_count": (i64, [vp]),
+        "mpmk_mg_init": (i, [vp, C.c_char_p, vp, i, i, i]),
+        "mpmk_mg_finalize": (i, [vp]),
+        "mpmk_mg_set_slab": (i, [vp, i, i, i, i, i, vp, vp]),
+        "mpmk_mg_halo_exchange": (i, [vp, vp]),
     }
+    L.mpmk_mg_unique_id.restype = i
+    L.mpmk_mg_unique_id.argtypes = [C.c_char_p, vp, i]
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
         fn.restype = res

@@ -27,10 +27,16 @@ class _Backend:
 
     F4 = ("xm", "vv", "c0", "c1", "cs", "s1", "f0", "f1", "f2", "cv0", "cv1")
 
-    def __init__(self, n_particles: int, n_grid: int, grid_extent: float, device: torch.device, capacity=None):
+    def __init__(self, n_particles: int, n_grid: int, grid_extent: float, device: torch.device, capacity=None,
+                 ids=None, n_global=None):
+        """capacity > n_particles leaves room for particles that migrate in (multi-GPU slabs, slabs.py);
+        ids / n_global: global particle ids of the local particles and the global particle count -- the
+        original-order arrays (init_cov, export buffers) are then indexed by global id."""
         _require_cuda()
         self.n = int(n_particles)
         self.capacity = int(capacity or n_particles)
+        self.ids_init = None if ids is None else ids.to(device=device, dtype=torch.int32)
+        self.n_global = int(n_global if n_global is not None else n_particles)
         self.n_grid = int(n_grid)
         self.device = device
         dev_index = device.index if device.index is not None else torch.cuda.current_device()
@@ -48,10 +54,11 @@ class _Backend:
         self.grid_in = z(g, g, g, 4)
         self.grid_out = z(g, g, g, 4)
         # original-order, cold
-        self.init_cov = z(max(self.n, 1), 6)
-        self.out_xyz = z(max(self.n, 1), 3)
-        self.out_cov = z(max(self.n, 1), 6)
-        self.out_R = z(max(self.n, 1), 3, 3)
+        ng = max(self.n_global, 1)
+        self.init_cov = z(ng, 6)
+        self.out_xyz = z(ng, 3)
+        self.out_cov = z(ng, 6)
+        self.out_R = z(ng, 3, 3)
         self.params = _native.Params()
         self._bind()
         self.export_fresh = False     # out_* hold postprocess() results of the current state
@@ -82,10 +89,18 @@ class _Backend:
         """original particle id of each physical slot (int64[n])"""
         return self.cur["meta"][: self.n, 0].long()
 
+    def local_ids(self):
+        """ids() for scattering into n-sized original-order tensors; slabs hold a subset of a global id
+        space, where the reference's per-field original-order view does not exist"""
+        if self.ids_init is not None:
+            raise _native.MpmkError("original-order field views are not available on a slab; use SlabSimulator.gather()/export()")
+        return self.ids()
+
     def reset_order(self):
         """physical order := original order, in set 0"""
         self.ctx.call("mpmk_set_count", self.n, 0)
-        self.sets[0]["meta"][: self.n, 0] = torch.arange(self.n, dtype=torch.int32, device=self.device)
+        self.sets[0]["meta"][: self.n, 0] = (self.ids_init[: self.n] if self.ids_init is not None else
+                                             torch.arange(self.n, dtype=torch.int32, device=self.device))
         self.sets[0]["meta"][: self.n, 3] = 0
 
     def invalidate(self):
@@ -132,7 +147,7 @@ class FieldView:
         b = self._b
         vals = self._gather_sorted().to(self._dtype)
         out = torch.empty_like(vals)
-        out[b.ids()] = vals
+        out[b.local_ids()] = vals
         out = out.reshape((b.n,) + self._tail)
         return out if device is None else out.to(device)
 
@@ -142,7 +157,7 @@ class FieldView:
     def from_torch(self, t):
         b = self._b
         t = t.to(device=b.device).reshape(b.n, -1)
-        vals = t[b.ids()]
+        vals = t[b.local_ids()]
         cur = b.cur
         for k, (a, c) in enumerate(self._cols):
             cur[a][: b.n, c] = vals[:, k].to(cur[a].dtype)
@@ -230,7 +245,7 @@ class _SymStressField(FieldView):
         six = self._gather_sorted()
         full = six[:, list(self.IDX)]
         out = torch.empty_like(full)
-        out[b.ids()] = full
+        out[b.local_ids()] = full
         out = out.reshape(b.n, 3, 3)
         return out if device is None else out.to(device)
 
@@ -374,6 +389,14 @@ class MPM_model:
         n = b.n
         if n == 0:
             return
+        if b.ids_init is not None:
+            # slab of a multi-GPU run: no per-particle E/nu modifiers there, the parameters are uniform
+            mu = torch.empty(1, dtype=torch.float32, device=b.device)
+            lam = torch.empty(1, dtype=torch.float32, device=b.device)
+            compute_mu_lam_from_E_nu(b.ctx, 1, self._logE[:1].contiguous(), self._y[:1].contiguous(), mu, lam)
+            self.mu.fill(float(mu.item()))
+            self.lam.fill(float(lam.item()))
+            return
         mu = torch.empty(n, dtype=torch.float32, device=b.device)
         lam = torch.empty(n, dtype=torch.float32, device=b.device)
         compute_mu_lam_from_E_nu(b.ctx, n, self._logE, self._y, mu, lam)
@@ -480,9 +503,13 @@ class MPM_state:
         cur["f0"][:n] = torch.tensor([1.0, 0.0, 0.0, 0.0], device=dev)
         cur["f1"][:n] = torch.tensor([1.0, 0.0, 0.0, 0.0], device=dev)
         cur["f2"][:n, 0] = 1.0
-        b.init_cov.copy_(covs.to(device=dev, dtype=torch.float32, non_blocking=True).reshape(n, 6))
-        cur["cv0"][:n] = b.init_cov[:, :4]
-        cur["cv1"][:n, :2] = b.init_cov[:, 4:]
+        c6 = covs.to(device=dev, dtype=torch.float32, non_blocking=True).reshape(n, 6)
+        if b.ids_init is not None:
+            b.init_cov[b.ids_init[:n].long()] = c6
+        else:
+            b.init_cov.copy_(c6)
+        cur["cv0"][:n] = c6[:, :4]
+        cur["cv1"][:n, :2] = c6[:, 4:]
         b._ftrial_valid = False
         b.invalidate()
         b.recompute_keys()

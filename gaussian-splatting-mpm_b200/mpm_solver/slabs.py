@@ -1,0 +1,395 @@
+"""Multi-GPU slab decomposition of the MPM substep: host side.
+
+The reference is single-GPU (one `ti.init(arch=ti.cuda)`, dense global fields: main.py:28,
+model.py:118-121); this module has no counterpart there.  One process per GPU (torchrun).  Rank r owns
+the base-cell planes [bounds[r], bounds[r+1]) of the grid's slowest axis (x) and simulates the
+particles whose base cell lies there with an ordinary `MPM_Simulator` over its own full-size grid
+arrays (touched sparsely).  Per substep the CUDA library exchanges the partial P2G sums of the planes
+shared with each neighbour (csrc/mg.cu: ncclSend/ncclRecv on the compute stream, symmetric add, both
+sides then run the grid update on them).  Between batches of `migrate_every` substeps this module
+moves the particles whose base cell left the slab to the neighbouring rank (torch.distributed P2P:
+NCCL over NVLink on GPUs, gloo in the CPU tests) -- a particle may sit up to `ghost` cells outside
+its owner's slab in between, which is what the shared region [x_hi-ghost, x_hi+ghost+2) allows for.
+
+Everything above `SlabSimulator` is device-agnostic torch code so that the partitioning and the
+migration protocol are exercised on CPU tensors by the world_size-2 gloo tests (tests/test_slabs.py).
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+RECORD_ARRAYS = ("xm", "vv", "c0", "c1", "cs", "s1", "f0", "f1", "f2", "meta", "cv0", "cv1")
+
+
+class SlabError(RuntimeError):
+    pass
+
+
+# ---- keys ---------------------------------------------------------------------------------------
+def key_base_xyz(keys: torch.Tensor, nt: int):
+    """base cell (bx, by, bz) from the cell key of csrc/common.cuh make_key: tile<<6 | lx<<4 | ly<<2 | lz"""
+    k = keys.to(torch.int64)
+    tile = k >> 6
+    tz = tile % nt
+    ty = (tile // nt) % nt
+    tx = tile // (nt * nt)
+    return 4 * tx + ((k >> 4) & 3), 4 * ty + ((k >> 2) & 3), 4 * tz + (k & 3)
+
+
+def base_cell_x(x: torch.Tensor, inv_dx: float, n_grid: int):
+    """utils.py:94-95 base cell of coordinate x in fp32: (int)(x*inv_dx - 0.5), clamped like the kernels"""
+    gp = x.to(torch.float32) * torch.tensor(inv_dx, dtype=torch.float32, device=x.device)
+    return (gp - 0.5).to(torch.int32).clamp_(0, n_grid - 3).to(torch.int64)
+
+
+# ---- slab bounds --------------------------------------------------------------------------------
+def uniform_bounds(n_grid: int, lo: int, hi: int, world: int, align: int = 4):
+    """`world` slabs of equal width over the occupied planes [lo, hi); the outer slabs extend to the grid
+    faces.  Interior cuts are multiples of `align` (the 4-cell tile edge) so no tile straddles a cut."""
+    cuts = [0]
+    for r in range(1, world):
+        c = lo + (hi - lo) * r / world
+        cuts.append(int(round(c / align)) * align)
+    cuts.append(n_grid)
+    return cuts
+
+
+def quantile_bounds(plane_hist: torch.Tensor, world: int, align: int = 4, min_width: int = 8):
+    """cuts at particle-count quantiles of the per-plane histogram of base-cell x (SURVEY.md 7.3-7:
+    compact scenes starve equal-width slabs), aligned to tiles and at least `min_width` planes wide"""
+    n = plane_hist.numel()
+    cum = torch.cumsum(plane_hist.to(torch.float64), 0)
+    total = float(cum[-1])
+    cuts = [0]
+    for r in range(1, world):
+        target = total * r / world
+        c = int(torch.searchsorted(cum, torch.tensor(target, dtype=torch.float64, device=cum.device)).item()) + 1
+        c = int(round(c / align)) * align
+        c = max(c, cuts[-1] + min_width)
+        cuts.append(c)
+    cuts.append(n)
+    for r in range(world - 1, 0, -1):  # keep the tail slabs wide enough too
+        cuts[r] = min(cuts[r], cuts[r + 1] - min_width)
+    if any(cuts[i + 1] - cuts[i] < min_width for i in range(world)):
+        raise SlabError(f"grid of {n} planes is too small for {world} slabs of >= {min_width} planes")
+    return cuts
+
+
+def shared_ranges(bounds, rank: int, ghost: int, n_grid: int):
+    """plane ranges whose P2G sums rank shares with rank-1 / rank+1 (mirrors mpmk_mg_set_slab)"""
+    world = len(bounds) - 1
+    x_lo, x_hi = bounds[rank], bounds[rank + 1]
+    lo = (max(0, x_lo - ghost), min(n_grid, x_lo + ghost + 2)) if rank > 0 else (0, 0)
+    hi = (max(0, x_hi - ghost), min(n_grid, x_hi + ghost + 2)) if rank < world - 1 else (0, 0)
+    return lo, hi
+
+
+def check_bounds(bounds, ghost: int):
+    for r in range(len(bounds) - 1):
+        if bounds[r + 1] - bounds[r] < 2 * ghost + 2:
+            raise SlabError(f"slab {r} = [{bounds[r]},{bounds[r + 1]}) is thinner than 2*ghost+2 = {2 * ghost + 2} planes")
+
+
+# ---- particle records ---------------------------------------------------------------------------
+def pack_records(store: dict, idx: torch.Tensor) -> torch.Tensor:
+    """rows idx of every packed array (16-byte records) plus the key, bit-cast to one int32 matrix"""
+    cols = [store[a][idx].view(torch.int32) for a in RECORD_ARRAYS]
+    cols.append(store["keys"][idx].view(torch.int32).reshape(-1, 1))
+    return torch.cat(cols, dim=1).contiguous()
+
+
+RECORD_WIDTH = 4 * len(RECORD_ARRAYS) + 1
+
+
+def unpack_records(store: dict, idx: torch.Tensor, rows: torch.Tensor):
+    for j, a in enumerate(RECORD_ARRAYS):
+        store[a][idx] = rows[:, 4 * j:4 * j + 4].contiguous().view(store[a].dtype)
+    store["keys"][idx] = rows[:, -1].contiguous().view(store["keys"].dtype)
+
+
+# ---- migration ----------------------------------------------------------------------------------
+def _base_xy_i32(keys: torch.Tensor, nt: int):
+    """(bx, by) of int32 keys without widening (one pass over 4 B per particle)"""
+    tile = keys >> 6
+    bx = (tile // (nt * nt)) * 4 + ((keys >> 4) & 3)
+    by = ((tile // nt) % nt) * 4 + ((keys >> 2) & 3)
+    return bx, by
+
+
+def _payload_exchange(send_lo, send_hi, n_from_lo, n_from_hi, rank, world, group, device):
+    """leavers to rank-1 / rank+1, arrivals from them; the counts are already known on every rank"""
+    recv_lo = torch.empty((n_from_lo, RECORD_WIDTH), dtype=torch.int32, device=device)
+    recv_hi = torch.empty((n_from_hi, RECORD_WIDTH), dtype=torch.int32, device=device)
+    ops = []
+    for peer, snd, rcv in ((rank - 1, send_lo, recv_lo), (rank + 1, send_hi, recv_hi)):
+        if not 0 <= peer < world:
+            continue
+        if snd.shape[0] > 0:
+            ops.append(dist.P2POp(dist.isend, snd, peer, group=group))
+        if rcv.shape[0] > 0:
+            ops.append(dist.P2POp(dist.irecv, rcv, peer, group=group))
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+    return recv_lo, recv_hi
+
+
+def migrate(store: dict, n: int, capacity: int, bounds, rank: int, ghost: int, nt: int, n_grid: int = None, group=None):
+    """Move the particles whose base-cell plane left [bounds[rank], bounds[rank+1]) to the neighbouring
+    rank and take in what the neighbours send.  `store` maps the packed array names (+ "keys") to tensors
+    of `capacity` records whose first `n` are live.  Holes left by leavers are refilled by arrivals and,
+    if the slab shrank, by live records from the tail, so the live records stay contiguous in [0, n_new)
+    (their order is irrelevant: every substep starts with a sort).
+
+    One collective and one host synchronisation: every rank contributes {leavers down, leavers up, particles
+    beyond the ghost margin, -min row, max row} to an all_gather, from which each rank reads its neighbours'
+    counts, the global error flag and the global row range.  Returns (n_new, stats)."""
+    world = len(bounds) - 1
+    x_lo, x_hi = bounds[rank], bounds[rank + 1]
+    device = store["keys"].device
+    n_grid = n_grid if n_grid is not None else 4 * nt
+    keys = store["keys"][:n]
+    if n > 0:
+        bx, by = _base_xy_i32(keys, nt)
+        lo_mask, hi_mask = bx < x_lo, bx >= x_hi
+        far = (bx < x_lo - ghost) | (bx >= x_hi + ghost)
+        mine = torch.stack([lo_mask.sum(), hi_mask.sum(), far.sum(), -by.min().to(torch.int64), by.max().to(torch.int64)])
+    else:
+        lo_mask = hi_mask = torch.zeros(0, dtype=torch.bool, device=device)
+        mine = torch.tensor([0, 0, 0, -n_grid, -1], dtype=torch.int64, device=device)
+    table = torch.empty(world * 5, dtype=torch.int64, device=device)
+    if world > 1:
+        dist.all_gather_into_tensor(table, mine.to(torch.int64).contiguous(), group=group)
+    else:
+        table[:5] = mine
+    table = table.view(world, 5).cpu()                    # the one synchronisation
+    if int(table[:, 2].sum()):
+        bad = [r for r in range(world) if int(table[r, 2])]
+        raise SlabError(f"ranks {bad}: particles drifted more than ghost={ghost} planes outside their slab between "
+                        "migrations; migrate more often or raise ghost")
+    n_lo, n_hi = int(table[rank, 0]), int(table[rank, 1])
+    n_from_lo = int(table[rank - 1, 1]) if rank > 0 else 0
+    n_from_hi = int(table[rank + 1, 0]) if rank < world - 1 else 0
+    y_min, y_max = -int(table[:, 3].max()), int(table[:, 4].max())
+    rows = (0, n_grid) if y_max < y_min else (max(0, y_min - ghost - 1), min(n_grid, y_max + 3 + ghost + 1))
+    stats = {"sent_lo": n_lo, "sent_hi": n_hi, "recv_lo": n_from_lo, "recv_hi": n_from_hi, "rows": rows}
+    if n_lo + n_hi + n_from_lo + n_from_hi == 0:
+        return n, stats
+    idx_lo = torch.nonzero_static(lo_mask, size=n_lo).flatten()
+    idx_hi = torch.nonzero_static(hi_mask, size=n_hi).flatten()
+    recv_lo, recv_hi = _payload_exchange(pack_records(store, idx_lo), pack_records(store, idx_hi), n_from_lo, n_from_hi,
+                                         rank, world, group, device)
+    holes = torch.cat([idx_lo, idx_hi])
+    arrivals = torch.cat([recv_lo, recv_hi])
+    n_new = n - holes.numel() + arrivals.shape[0]
+    if n_new > capacity:
+        raise SlabError(f"rank {rank}: {n_new} particles after migration exceed the capacity {capacity}")
+    free = [holes[holes < n_new]]
+    rows_in = [arrivals]
+    if n_new > n:
+        free.append(torch.arange(n, n_new, device=device))
+    elif n_new < n:
+        tail_is_hole = torch.zeros(n - n_new, dtype=torch.bool, device=device)
+        tail_is_hole[holes[holes >= n_new] - n_new] = True
+        live_tail = torch.nonzero(~tail_is_hole).flatten() + n_new
+        rows_in.append(pack_records(store, live_tail))
+    free = torch.cat(free)
+    rows_in = torch.cat(rows_in)
+    if free.numel() != rows_in.shape[0]:
+        raise SlabError(f"rank {rank}: migration bookkeeping mismatch ({free.numel()} free slots, {rows_in.shape[0]} records)")
+    if free.numel():
+        unpack_records(store, free, rows_in)
+    return n_new, stats
+
+
+def global_row_range(store: dict, n: int, nt: int, n_grid: int, margin: int, group=None):
+    """[y_lo, y_hi): rows of the shared planes any rank's stencils can reach before the next migration"""
+    device = store["keys"].device
+    if n > 0:
+        _, by = _base_xy_i32(store["keys"][:n], nt)
+        lo, hi = by.min().to(torch.int64), by.max().to(torch.int64)
+    else:
+        lo = torch.tensor(n_grid, dtype=torch.int64, device=device)
+        hi = torch.tensor(-1, dtype=torch.int64, device=device)
+    v = torch.stack([-lo, hi]).to(torch.int64)
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(v, op=dist.ReduceOp.MAX, group=group)
+    lo, hi = -int(v[0].item()), int(v[1].item())
+    if hi < lo:
+        return 0, n_grid
+    return max(0, lo - margin), min(n_grid, hi + 3 + margin)
+
+
+# ---- the per-rank simulator -----------------------------------------------------------------------
+class SlabSimulator:
+    """One rank's share of a slab-decomposed simulation: an `MPM_Simulator` over the local particles plus
+    the halo/migration plumbing.  Construct it on every rank of an initialised torch.distributed group
+    (backend nccl) with that rank's particles:
+
+        ids      global particle ids of the local particles (int, unique across ranks)
+        n_global total number of particles over all ranks
+        bounds   world+1 plane cuts (uniform_bounds / quantile_bounds), identical on every rank
+    """
+
+    def __init__(self, xyz, cov, vol, args, ids, n_global, bounds, vel=None, group=None, ghost=1, migrate_every=10,
+                 capacity=None, boundary_conditions=None, collider=None, **sim_kw):
+        from . import _native
+        from .solver import MPM_Simulator
+        from .utils import _stream
+        self._native, self._stream = _native, _stream
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.bounds = [int(b) for b in bounds]
+        if len(self.bounds) != self.world + 1:
+            raise SlabError("bounds must hold world+1 cuts")
+        self.ghost = int(ghost)
+        check_bounds(self.bounds, self.ghost)
+        self.migrate_every = int(migrate_every)
+        self.n_global = int(n_global)
+        n = int(xyz.shape[0])
+        cap = int(capacity if capacity is not None else max(int(1.25 * n) + 4096, 8192))
+        self.sim = MPM_Simulator(xyz, cov, vol, args, capacity=cap, ids=ids, n_global=n_global, **sim_kw)
+        b = self.backend = self.sim._backend
+        self.device = b.device
+        self.n_grid = int(args.n_grid)
+        self.nt = (self.n_grid + 3) // 4
+        if vel is not None and n:
+            b.cur["vv"][:n, :3] = vel.to(device=self.device, dtype=torch.float32)
+        if boundary_conditions:
+            self.sim.set_boundary_conditions(boundary_conditions, args)
+        if collider:
+            self.sim.add_surface_collider(collider["point"], collider["normal"], friction=collider.get("friction", 0.0))
+        # communicator of the halo data path: rank 0 makes the NCCL id, torch.distributed carries it
+        lib_path = _native.nccl_library_path().encode()
+        uid = torch.zeros(_native.NCCL_ID_BYTES, dtype=torch.uint8)
+        if self.rank == 0:
+            import ctypes as C
+            buf = (C.c_char * _native.NCCL_ID_BYTES)()
+            rc = _native.lib().mpmk_mg_unique_id(lib_path, C.cast(buf, C.c_void_p), _native.NCCL_ID_BYTES)
+            if rc != 0:
+                raise SlabError("mpmk_mg_unique_id failed")
+            uid = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8).clone()
+        uid = uid.to(self.device)
+        dist.broadcast(uid, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        self._uid = bytes(uid.cpu().numpy().tobytes())
+        b.ctx.call("mpmk_mg_init", lib_path, self._uid, _native.NCCL_ID_BYTES, self.rank, self.world)
+        planes = 2 * self.ghost + 2
+        z = lambda: torch.zeros((planes * self.n_grid * self.n_grid, 4), dtype=torch.float32, device=self.device)
+        self._recv_lo = z() if self.rank > 0 else None
+        self._recv_hi = z() if self.rank < self.world - 1 else None
+        self.stats = {"migrations": 0, "sent": 0, "received": 0}
+        self._since_migration = 0
+        self._replicate_init_cov()
+        self._set_slab()
+
+    # -- plumbing ---------------------------------------------------------------------------------
+    @property
+    def n_particles(self):
+        return self.backend.n
+
+    def _store(self):
+        b = self.backend
+        st = dict(b.cur)
+        st["keys"] = b.keys
+        return st
+
+    def _replicate_init_cov(self):
+        """export needs Sigma_0 of whatever particle a rank holds after migrations: every rank wrote the rows
+        of its own ids (zeros elsewhere), the sum makes the table complete on all ranks"""
+        dist.all_reduce(self.backend.init_cov, group=self.group)
+
+    def _set_slab(self, rows=None):
+        b = self.backend
+        y_lo, y_hi = rows if rows is not None else global_row_range(self._store(), b.n, self.nt, self.n_grid, self.ghost + 1, self.group)
+        self.rows = (y_lo, y_hi)
+        b.ctx.call("mpmk_mg_set_slab", self.bounds[self.rank], self.bounds[self.rank + 1], self.ghost, y_lo, y_hi,
+                   self._recv_lo.data_ptr() if self._recv_lo is not None else None,
+                   self._recv_hi.data_ptr() if self._recv_hi is not None else None)
+
+    def migrate(self):
+        b = self.backend
+        n_new, st = migrate(self._store(), b.n, b.capacity, self.bounds, self.rank, self.ghost, self.nt, self.n_grid, self.group)
+        b.n = n_new
+        self.sim.n_particles = n_new
+        b.ctx.call("mpmk_set_count", n_new, b.ctx.L.mpmk_current_set(b.ctx.h))
+        b.invalidate()
+        self.stats["migrations"] += 1
+        self.stats["sent"] += st["sent_lo"] + st["sent_hi"]
+        self.stats["received"] += st["recv_lo"] + st["recv_hi"]
+        self._since_migration = 0
+        self._set_slab(st["rows"])
+        return st
+
+    def reload(self, xyz, cov, vol, vel, ids):
+        """re-initialise this rank's particles in place from new data (the constructor's state
+        initialisation, model.py:101-115, without reallocating); registered grid operations stay"""
+        b = self.backend
+        n = int(xyz.shape[0])
+        if n > b.capacity:
+            raise SlabError("reload: more particles than capacity")
+        b.n = n
+        self.sim.n_particles = n
+        b.ids_init = ids.to(device=self.device, dtype=torch.int32)
+        b.init_cov.zero_()
+        self.sim.mpm_state._init_particles(xyz, cov, vol)
+        self._replicate_init_cov()
+        self.sim.mpm_model._reinit_packed()
+        b.cur["vv"][:n, :3] = vel.to(device=self.device, dtype=torch.float32)
+        self.sim.time = 0.0
+        self.sim._sync_flags()
+        self._since_migration = 0
+        self._set_slab()
+
+    # -- stepping ---------------------------------------------------------------------------------
+    def step(self, n_substeps, dt=None):
+        """n_substeps substeps (MPM_Simulator.step, whose substeps now include the halo sum), with a
+        migration after every `migrate_every` of them"""
+        done = 0
+        while done < n_substeps:
+            k = min(n_substeps - done, self.migrate_every - self._since_migration)
+            self.sim.step(k, dt)
+            done += k
+            self._since_migration += k
+            if self._since_migration >= self.migrate_every:
+                self.migrate()
+
+    def p2g2p(self, dt):
+        self.step(1, dt)
+
+    # -- results ----------------------------------------------------------------------------------
+    def gather(self):
+        """(ids, xyz, vel, F) of the local particles in physical order"""
+        b = self.backend
+        n, cur = b.n, b.cur
+        F = torch.cat([cur["f0"][:n], cur["f1"][:n], cur["f2"][:n, :1]], dim=1).reshape(n, 3, 3)
+        return cur["meta"][:n, 0].long(), cur["xm"][:n, :3].clone(), cur["vv"][:n, :3].clone(), F
+
+    def export(self):
+        """postprocess() on every rank, summed into complete (xyz [N,3], cov [N,6], R [N,3,3]) tensors in
+        global id order on every rank (each id is written by exactly one rank; the others hold zeros)"""
+        b = self.backend
+        for t in (b.out_xyz, b.out_cov, b.out_R):
+            t.zero_()
+        b.export(want_R=True)
+        for t in (b.out_xyz, b.out_cov, b.out_R):
+            dist.all_reduce(t, group=self.group)
+        return b.out_xyz, b.out_cov, b.out_R
+
+    def global_count(self):
+        t = torch.tensor([self.backend.n], dtype=torch.int64, device=self.device)
+        dist.all_reduce(t, group=self.group)
+        return int(t.item())
+
+    def close(self):
+        self.backend.ctx.call("mpmk_mg_finalize")
+
+
+def partition_cloud(cloud: dict, bounds, rank: int, inv_dx: float, n_grid: int):
+    """the rows of a host-side cloud (numpy dict xyz/vel/cov/vol) whose base-cell plane lies in this rank's
+    slab, plus their global ids"""
+    import numpy as np
+    bx = base_cell_x(torch.from_numpy(cloud["xyz"][:, 0].copy()), inv_dx, n_grid).numpy()
+    sel = np.nonzero((bx >= bounds[rank]) & (bx < bounds[rank + 1]))[0]
+    return {k: v[sel] for k, v in cloud.items()}, sel.astype(np.int64)

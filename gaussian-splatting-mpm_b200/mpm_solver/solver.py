@@ -42,12 +42,14 @@ ti = _TiShim()
 
 
 class MPM_Simulator:
-    def __init__(self, xyzs, covs, volumes, args, init_v=None, strict_q1=True, strict_q3=True, track_cov=False):
+    def __init__(self, xyzs, covs, volumes, args, init_v=None, strict_q1=True, strict_q3=True, track_cov=False,
+                 capacity=None, ids=None, n_global=None):
         if getattr(args, "fitting", False):
             raise NotImplementedError("differentiable path (MPM_state_opt) out of scope")
         self.n_particles = xyzs.shape[0]
         device = xyzs.device if xyzs.is_cuda else torch.device("cuda", torch.cuda.current_device())
-        self._backend = _Backend(self.n_particles, args.n_grid, args.grid_extent, device)
+        self._backend = _Backend(self.n_particles, args.n_grid, args.grid_extent, device, capacity=capacity, ids=ids,
+                                 n_global=n_global)
         self.mpm_model = MPM_model(self.n_particles, args, _backend=self._backend)
         self.mpm_state = MPM_state(self.n_particles, xyzs, covs, volumes, args, _backend=self._backend)
 

@@ -1,0 +1,160 @@
+"""Multi-GPU slab host logic (mpm_solver/slabs.py).  CPU: bounds, key decoding and the migration protocol
+over gloo with world_size 2 and 3.  GPU (needs >= 2 devices): a 2-rank run against the 1-GPU run."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from mpm_solver import slabs
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def np_make_key(bx, by, bz, nt):
+    tile = ((bx >> 2) * nt + (by >> 2)) * nt + (bz >> 2)
+    return (tile << 6) | ((bx & 3) << 4) | ((by & 3) << 2) | (bz & 3)
+
+
+def test_key_decode_roundtrip():
+    rng = np.random.default_rng(0)
+    for n_grid in (50, 64, 512):
+        nt = (n_grid + 3) // 4
+        b = rng.integers(0, n_grid - 2, size=(1000, 3))
+        keys = torch.from_numpy(np_make_key(b[:, 0], b[:, 1], b[:, 2], nt).astype(np.int32))
+        bx, by, bz = slabs.key_base_xyz(keys, nt)
+        assert np.array_equal(bx.numpy(), b[:, 0]) and np.array_equal(by.numpy(), b[:, 1]) and np.array_equal(bz.numpy(), b[:, 2])
+
+
+def test_base_cell_matches_kernel_expression():
+    x = torch.tensor([0.0, 0.0039, 0.5, 0.7771, 1.999], dtype=torch.float32)
+    inv_dx = 256 / 2.0
+    want = np.clip((x.numpy() * np.float32(inv_dx) - np.float32(0.5)).astype(np.int32), 0, 253)
+    assert np.array_equal(slabs.base_cell_x(x, inv_dx, 256).numpy(), want)
+
+
+def test_bounds():
+    b = slabs.uniform_bounds(512, 32, 480, 8)
+    assert b[0] == 0 and b[-1] == 512 and len(b) == 9 and all(c % 4 == 0 for c in b)
+    assert all(b[i + 1] - b[i] >= 56 for i in range(8))
+    slabs.check_bounds(b, ghost=2)
+    with pytest.raises(slabs.SlabError):
+        slabs.check_bounds([0, 3, 64], ghost=1)
+    hist = torch.zeros(64)
+    hist[20:28] = 100.0   # a compact blob: equal-width slabs would leave two of four ranks empty
+    hist[28:44] = 10.0
+    q = slabs.quantile_bounds(hist, 4, align=4, min_width=4)
+    assert q[0] == 0 and q[-1] == 64 and all(q[i + 1] - q[i] >= 4 for i in range(4))
+    per = [float(hist[q[i]:q[i + 1]].sum()) for i in range(4)]
+    assert min(per) > 0
+    lo, hi = slabs.shared_ranges([0, 32, 64], 0, ghost=1, n_grid=64)
+    assert lo == (0, 0) and hi == (31, 35)
+    lo, hi = slabs.shared_ranges([0, 32, 64], 1, ghost=1, n_grid=64)
+    assert lo == (31, 35) and hi == (0, 0)
+
+
+# ---- migration over gloo ----------------------------------------------------------------------------
+def _fake_store(rank, bounds, n, cap, nt, n_grid, ghost, seed):
+    """n live records owned by `rank`, of which some have drifted up to `ghost` planes outside the slab"""
+    rng = np.random.default_rng(seed + rank)
+    world = len(bounds) - 1
+    lo = bounds[rank] - (ghost if rank > 0 else 0)
+    hi = bounds[rank + 1] + (ghost if rank < world - 1 else 0)
+    hi = min(hi, n_grid - 2)
+    bx = rng.integers(lo, hi, size=n)
+    by = rng.integers(8, 24, size=n)
+    bz = rng.integers(0, n_grid - 2, size=n)
+    store = {}
+    for j, a in enumerate(slabs.RECORD_ARRAYS):
+        if a == "meta":
+            t = torch.zeros((cap, 4), dtype=torch.int32)
+            t[:n, 0] = torch.arange(n, dtype=torch.int32) + 1_000_000 * rank   # global id
+            t[:n, 1] = rank
+        else:
+            t = torch.zeros((cap, 4), dtype=torch.float32)
+            t[:n] = torch.from_numpy(rng.standard_normal((n, 4)).astype(np.float32))
+        store[a] = t
+    store["keys"] = torch.zeros(cap, dtype=torch.int32)
+    store["keys"][:n] = torch.from_numpy(np_make_key(bx, by, bz, nt).astype(np.int32))
+    return store
+
+
+def _migrate_worker(rank, world, port, bounds, n_per, cap, n_grid, ghost, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        nt = (n_grid + 3) // 4
+        store = _fake_store(rank, bounds, n_per[rank], cap, nt, n_grid, ghost, seed=11)
+        before = slabs.pack_records(store, torch.arange(n_per[rank])).numpy().copy()
+        n_new, st = slabs.migrate(store, n_per[rank], cap, bounds, rank, ghost, nt, n_grid)
+        after = slabs.pack_records(store, torch.arange(n_new)).numpy().copy()
+        rows = slabs.global_row_range(store, n_new, nt, n_grid, ghost + 1)
+        assert rows == st["rows"]   # migration moves particles between ranks, the global row range is unchanged
+        q.put((rank, before, after, st, rows))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n_per", [(2, [4000, 2500]), (3, [3000, 10, 5000]), (2, [0, 700])])
+def test_migration_protocol_gloo(world, n_per):
+    n_grid, ghost = 64, 2
+    bounds = slabs.uniform_bounds(n_grid, 8, 56, world)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() % 2000) + world
+    procs = [ctx.Process(target=_migrate_worker, args=(r, world, port, bounds, n_per, 8192, n_grid, ghost, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = {}
+    for _ in range(world):
+        r, before, after, st, rows = q.get(timeout=60)
+        res[r] = (before, after, st, rows)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    nt = (n_grid + 3) // 4
+    id_col = 4 * slabs.RECORD_ARRAYS.index("meta")
+    all_before = np.concatenate([res[r][0] for r in range(world)])
+    all_after = np.concatenate([res[r][1] for r in range(world)])
+    # nothing lost, nothing duplicated, every record bit-identical
+    assert all_before.shape == all_after.shape
+    ob, oa = np.argsort(all_before[:, id_col], kind="stable"), np.argsort(all_after[:, id_col], kind="stable")
+    assert np.array_equal(all_before[ob], all_after[oa])
+    assert len(np.unique(all_after[:, id_col])) == all_after.shape[0]
+    # every particle now sits on the rank that owns its base-cell plane
+    moved = 0
+    for r in range(world):
+        after = res[r][1]
+        bx, _, _ = slabs.key_base_xyz(torch.from_numpy(after[:, -1].copy()), nt)
+        assert bool(((bx >= bounds[r]) & (bx < bounds[r + 1])).all())
+        moved += res[r][2]["sent_lo"] + res[r][2]["sent_hi"]
+        assert res[r][3] == res[0][3]   # the row range is agreed on by all ranks
+    assert moved > 0
+    assert sum(res[r][2]["sent_lo"] + res[r][2]["sent_hi"] for r in range(world)) == \
+        sum(res[r][2]["recv_lo"] + res[r][2]["recv_hi"] for r in range(world))
+
+
+def test_migration_rejects_excess_drift():
+    """a particle more than `ghost` planes outside its slab has been scattering outside the shared region"""
+    nt = 16
+    store = _fake_store(0, [0, 64], 10, 16, nt, 64, 0, seed=3)
+    store["keys"][0] = int(np_make_key(np.array(40), np.array(9), np.array(9), nt))
+    with pytest.raises(slabs.SlabError):
+        slabs.migrate(store, 10, 16, [0, 36], 0, 2, nt, 64)   # one slab [0,36): plane 40 is beyond 36 + ghost
+
+
+# ---- two GPUs against one -----------------------------------------------------------------------------
+@pytest.mark.gpu
+def test_two_rank_run_matches_single_gpu():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29631", os.path.join(ROOT, "tests", "mg_parity.py")]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
+    assert "mg parity ok" in out.stdout
