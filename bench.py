@@ -140,7 +140,7 @@ def run_reference(a, rank, world):
 def run_multi(a, rank, world, local, dev):
     """N > 1: the S-32M-bar cloud scaled to N ranks (weak scaling: every rank owns a 56 x 96 x 96-cell block of
     the bar = 4,128,768 particles on the 512^3 grid), slab-decomposed along x (mpm_solver/slabs.py): per-substep
-    NCCL halo sum of the shared planes, particle migration once per step."""
+    NCCL halo sum of the shared planes, particle migration every k substeps (k chosen from the particle speeds)."""
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -162,7 +162,7 @@ def run_multi(a, rank, world, local, dev):
     pin = {k: torch.from_numpy(v).pin_memory() for k, v in cloud.items()}
     ids = (torch.arange(n0, dtype=torch.int64) + rank * n0).to(dev)
     up = lambda k: pin[k].to(dev, non_blocking=True)
-    sl = slabs.SlabSimulator(up("xyz"), up("cov"), up("vol"), args, ids, N, bounds, vel=up("vel"), ghost=1, migrate_every=(a.migrate_every or S),
+    sl = slabs.SlabSimulator(up("xyz"), up("cov"), up("vol"), args, ids, N, bounds, vel=up("vel"), ghost=2, migrate_every=(a.migrate_every or "auto"),
                              boundary_conditions=ops["boundary_conditions"], collider=ops["collider"], strict_q1=False)
     stream = torch.cuda.current_stream()
 
@@ -171,14 +171,23 @@ def run_multi(a, rank, world, local, dev):
         dist.barrier()
         torch.cuda.synchronize()
 
+    step_ms = []
+
     def timed(fn, k):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        marks = [torch.cuda.Event(enable_timing=True) for _ in range(k)]
         e0.record(stream)
-        for _ in range(k):
+        for i in range(k):
             fn()
+            marks[i].record(stream)
         e1.record(stream)
         barrier()
+        prev = e0
+        del step_ms[:]
+        for m in marks:
+            step_ms.append(round(prev.elapsed_time(m), 3))
+            prev = m
         t = torch.tensor([e0.elapsed_time(e1)], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)   # device time, max over ranks
         return float(t.item())
@@ -193,6 +202,7 @@ def run_multi(a, rank, world, local, dev):
     t0 = time.time()
     ms = timed(lambda: sl.step(S, dt), a.steps)
     t1 = time.time()
+    resident_step_ms = list(step_ms)
     launches = L.mpmk_launch_count(h) - l0
     clocks = sampler.stop(t0, t1) if sampler else None
     assert sl.global_count() == N
@@ -220,6 +230,8 @@ def run_multi(a, rank, world, local, dev):
     peak, peak_src = _peaks()
     sub_bytes = 216.0 * N + 72.0 * float(touched.item())
     allin_ms = ms / (a.steps * S)
+    if rank == 0 and os.environ.get("MPMK_SLAB_TIMING"):
+        print("migration phases (ms per call):", slabs.timing_report(), file=sys.stderr, flush=True)
     if rank == 0:
         ach = sub_bytes / (allin_ms * 1e-3) / 1e9 / world
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
@@ -228,9 +240,10 @@ def run_multi(a, rank, world, local, dev):
                 "config": {"workload": f"S-32M-bar/{world} ({wx * world}x{wy}x{wz} cells of a 512^3 grid)", "particles": N,
                            "particles_per_gpu": n0, "n_grid": n_grid, "particles_per_cell": 8,
                            "material": a.material + (" (FCR, intended mode)" if a.material == "jelly" else ""),
-                           "substeps_per_step": S, "substep_dt": dt, "migrations_per_step": 1,
+                           "substeps_per_step": S, "substep_dt": dt, "ghost_planes": 2,
+                           "migration": f"every {sl.migrate_every} substeps (auto: half the ghost margin at the measured max speed)",
                            "l2": "particle state >> 126 MB L2 per GPU: inputs larger than L2, no flush needed",
-                           "parallelism": f"slab{world} (x-slabs, NCCL halo sum per substep, P2P migration per step)"},
+                           "parallelism": f"slab{world} (x-slabs, NCCL halo sum per substep, P2P migration)"},
                 "roofline": {"bound": "hbm", "kernel": "substep (all kernels, per GPU)", "achieved": ach, "peak": peak, "unit": "GB/s",
                              "frac": ach / peak, "traffic": None, "peak_source": peak_src,
                              "algorithmic_bytes_per_launch": sub_bytes / world,
@@ -239,7 +252,8 @@ def run_multi(a, rank, world, local, dev):
                 "e2e": {"value": N * S * ke / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": n0 * 13 * 4 * world,
                         "d2h_bytes_per_step": n0 * 9 * 4 * world, "ms_per_step": e2e_ms / ke, "steps": ke,
                         "what": "per rank: reload(host xyz,cov,vol,vel) + step(S) incl. migration + postprocess + D2H xyz,cov"},
-                "gpu_launches": int(launches), "migrated_particles": int(moved.item()), "clocks": clocks}
+                "gpu_launches": int(launches), "migrated_particles": int(moved.item()), "step_ms_rank0": resident_step_ms,
+                "clocks": clocks}
         print(json.dumps(line), flush=True)
     sl.close()
     dist.barrier()
@@ -256,7 +270,7 @@ def main():
     ap.add_argument("--material", default="jelly")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--substeps", type=int, default=SUBSTEPS_PER_STEP)
-    ap.add_argument("--migrate-every", type=int, default=0, help="N>1 tuning aid: substeps between migrations (default: one per step)")
+    ap.add_argument("--migrate-every", type=int, default=0, help="N>1: substeps between migrations (default 0 = auto from the measured particle speeds)")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -118,6 +118,17 @@ extern "C" int mpmk_mg_set_slab(mpmk_ctx* ctx, int x_lo, int x_hi, int ghost, in
     return 0;
 }
 
+// after a migration: the live count changed, everything else (current set, F_trial validity) stands --
+// the host moved the F_trial records together with the particle records
+extern "C" int mpmk_mg_set_count(mpmk_ctx* ctx, int64_t n) {
+    if (!ctx) return MPMK_ERR_INVALID;
+    if (n < 0 || n > ctx->capacity) MPMK_FAIL(ctx, MPMK_ERR_INVALID, "mpmk_mg_set_count: n=%lld capacity=%lld", (long long)n, (long long)ctx->capacity);
+    ctx->n = n;
+    ctx->sorted_valid = false;
+    ctx->prepared = false;
+    return 0;
+}
+
 // ---- kernels ----------------------------------------------------------------------------
 // region = planes [x0, x0+nx) x rows [y0, y0+ny) x all z; `buf` is the dense [nx][ny][n] exchange buffer
 __global__ void k_halo_add(float4* __restrict__ gin, const float4* __restrict__ buf, int x0, int nx, int y0, int ny, int n) {
@@ -186,4 +197,193 @@ int mpmk_mg_halo_sum(mpmk_ctx* ctx, cudaStream_t s) {
 extern "C" int mpmk_mg_halo_exchange(mpmk_ctx* ctx, void* stream) {
     if (!ctx || !ctx->bound) return MPMK_ERR_STATE;
     return mpmk_mg_halo_sum(ctx, (cudaStream_t)stream);
+}
+
+// ---- migration helpers (the protocol itself is mpm_solver/slabs.py) ------------------------------------------
+// stats layout (int32[8]): {leavers down, leavers up, beyond ghost, -min row, max row, max(|v_x|,|v_y|) (float bits), 0, 0}
+struct MgRecordPtrs {
+    const float4* src[16];
+    float4* dst[16];
+    int n_arrays;
+};
+
+__global__ void k_mg_stats_init(int* stats, int n_grid) {
+    if (threadIdx.x < 8) stats[threadIdx.x] = (threadIdx.x == 3) ? -n_grid : (threadIdx.x == 4 ? -1 : 0);
+}
+
+__global__ void __launch_bounds__(256) k_mg_scan(const uint32_t* __restrict__ keys, const float4* __restrict__ vv, int64_t n, int nt,
+                                                 int x_lo, int x_hi, int ghost, int* __restrict__ stats,
+                                                 int* __restrict__ idx_lo, int* __restrict__ idx_hi) {
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned lane = threadIdx.x & 31;
+    int by = -1, nby = -(1 << 30), far = 0;
+    float av = 0.f;
+    bool lo = false, hi = false;
+    if (p < n) {
+        const uint32_t k = keys[p];
+        const uint32_t tile = k >> 6;
+        const int bx = (int)(tile / (uint32_t)(nt * nt)) * 4 + (int)((k >> 4) & 3u);
+        by = (int)((tile / (uint32_t)nt) % (uint32_t)nt) * 4 + (int)((k >> 2) & 3u);
+        nby = -by;
+        lo = bx < x_lo; hi = bx >= x_hi;
+        far = (bx < x_lo - ghost || bx >= x_hi + ghost) ? 1 : 0;
+        const float4 v = vv[p];
+        av = fmaxf(fabsf(v.x), fabsf(v.y));   // drift along the slab axis and along the rows of the exchange window
+    }
+    // leavers: one atomic per warp and direction, order inside the lists is irrelevant
+    const unsigned mlo = __ballot_sync(0xffffffffu, lo), mhi = __ballot_sync(0xffffffffu, hi);
+    if (mlo) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&stats[0], __popc(mlo));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (lo) idx_lo[base + __popc(mlo & ((1u << lane) - 1u))] = (int)p;
+    }
+    if (mhi) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&stats[1], __popc(mhi));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (hi) idx_hi[base + __popc(mhi & ((1u << lane) - 1u))] = (int)p;
+    }
+    far = __reduce_add_sync(0xffffffffu, far);
+    nby = __reduce_max_sync(0xffffffffu, nby);
+    by = __reduce_max_sync(0xffffffffu, by);
+    int avb = __reduce_max_sync(0xffffffffu, __float_as_int(av));   // non-negative floats order like their bits
+    if (lane == 0) {
+        if (far) atomicAdd(&stats[2], far);
+        atomicMax(&stats[3], nby);
+        atomicMax(&stats[4], by);
+        atomicMax(&stats[5], avb);
+    }
+}
+
+// rows[count][n_arrays*4 + 1]: the 16-byte records of every array, then the key
+__global__ void __launch_bounds__(256) k_mg_pack(MgRecordPtrs P, const uint32_t* __restrict__ keys, const int* __restrict__ idx,
+                                                 int64_t count, int* __restrict__ rows) {
+    const int W = P.n_arrays * 4 + 1;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t r = t / (P.n_arrays + 1);
+    const int a = (int)(t % (P.n_arrays + 1));
+    if (r >= count) return;
+    const int slot = idx[r];
+    if (a < P.n_arrays) {
+        const float4 v = P.src[a][slot];
+        int* o = rows + r * W + 4 * a;
+        o[0] = __float_as_int(v.x); o[1] = __float_as_int(v.y); o[2] = __float_as_int(v.z); o[3] = __float_as_int(v.w);
+    } else {
+        rows[r * W + W - 1] = (int)keys[slot];
+    }
+}
+
+__global__ void __launch_bounds__(256) k_mg_unpack(MgRecordPtrs P, uint32_t* __restrict__ keys, const int* __restrict__ idx,
+                                                   int64_t idx_offset, int64_t count, const int* __restrict__ rows) {
+    // destination slot of row r: idx[r] when an index list is given, else idx_offset + r (append)
+    const int W = P.n_arrays * 4 + 1;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t r = t / (P.n_arrays + 1);
+    const int a = (int)(t % (P.n_arrays + 1));
+    if (r >= count) return;
+    const int64_t slot = idx ? (int64_t)idx[r] : idx_offset + r;
+    if (a < P.n_arrays) {
+        const int* i = rows + r * W + 4 * a;
+        P.dst[a][slot] = make_float4(__int_as_float(i[0]), __int_as_float(i[1]), __int_as_float(i[2]), __int_as_float(i[3]));
+    } else {
+        keys[slot] = (uint32_t)rows[r * W + W - 1];
+    }
+}
+
+// closing the holes a shrinking slab leaves below n_new: pass 1 splits the unfilled holes into those below n_new
+// (list) and those in the tail [n_new, n) (flags); pass 2 moves each live tail record into one of the listed holes
+__global__ void k_mg_split_holes(const int* __restrict__ holes, int64_t count, int64_t n_new, int* __restrict__ low_holes,
+                                 int* __restrict__ counters, unsigned char* __restrict__ tail_flag) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    const int h = holes[t];
+    if (h < n_new) low_holes[atomicAdd(&counters[0], 1)] = h;
+    else tail_flag[h - n_new] = 1;
+}
+
+__global__ void k_mg_move_tail(MgRecordPtrs P, uint32_t* __restrict__ keys, int64_t n_new, int64_t tail_len,
+                               const int* __restrict__ low_holes, int* __restrict__ counters,
+                               const unsigned char* __restrict__ tail_flag) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= tail_len || tail_flag[t]) return;
+    const int dst = low_holes[atomicAdd(&counters[1], 1)];
+    const int64_t src = n_new + t;
+    for (int a = 0; a < P.n_arrays; ++a) P.dst[a][dst] = P.src[a][src];
+    keys[dst] = keys[src];
+}
+
+static MgRecordPtrs record_ptrs(mpmk_ctx* ctx) {
+    // order = mpm_solver/slabs.py RECORD_ARRAYS
+    const mpmk_particle_set& s = ctx->b.set[ctx->cur];
+    void* arr[15] = {s.xm, s.vv, s.c0, s.c1, s.cs, s.s1, s.f0, s.f1, s.f2, s.meta, s.cv0, s.cv1, ctx->b.ft0, ctx->b.ft1, ctx->b.ft2};
+    MgRecordPtrs P;
+    P.n_arrays = 15;
+    for (int i = 0; i < 15; ++i) { P.src[i] = (const float4*)arr[i]; P.dst[i] = (float4*)arr[i]; }
+    P.src[15] = nullptr; P.dst[15] = nullptr;
+    return P;
+}
+
+#define REQUIRE_SLAB(ctx)                                                                          \
+    do {                                                                                           \
+        if (!(ctx) || !(ctx)->bound) return MPMK_ERR_STATE;                                        \
+        if ((ctx)->mg.world < 1) MPMK_FAIL(ctx, MPMK_ERR_STATE, "call mpmk_mg_init / mpmk_mg_set_slab first"); \
+    } while (0)
+
+extern "C" int mpmk_mg_scan(mpmk_ctx* ctx, void* stats_dev, void* idx_lo_dev, void* idx_hi_dev, void* stream) {
+    REQUIRE_SLAB(ctx);
+    cudaStream_t s = (cudaStream_t)stream;
+    const MgState& m = ctx->mg;
+    k_mg_stats_init<<<1, 32, 0, s>>>((int*)stats_dev, ctx->n_grid);
+    MPMK_LAUNCH_CHECK(ctx);
+    if (ctx->n > 0) {
+        k_mg_scan<<<div_up(ctx->n, 256), 256, 0, s>>>((const uint32_t*)ctx->b.keys, (const float4*)ctx->b.set[ctx->cur].vv, ctx->n,
+                                                      ctx->nt, m.x_lo, m.x_hi, m.ghost, (int*)stats_dev, (int*)idx_lo_dev,
+                                                      (int*)idx_hi_dev);
+        MPMK_LAUNCH_CHECK(ctx);
+    }
+    return 0;
+}
+
+extern "C" int mpmk_mg_pack(mpmk_ctx* ctx, const void* idx_dev, int64_t count, void* rows_dev, void* stream) {
+    REQUIRE_SLAB(ctx);
+    if (count <= 0) return 0;
+    const MgRecordPtrs P = record_ptrs(ctx);
+    k_mg_pack<<<div_up(count * (P.n_arrays + 1), 256), 256, 0, (cudaStream_t)stream>>>(P, (const uint32_t*)ctx->b.keys,
+                                                                                         (const int*)idx_dev, count, (int*)rows_dev);
+    MPMK_LAUNCH_CHECK(ctx);
+    return 0;
+}
+
+extern "C" int mpmk_mg_unpack(mpmk_ctx* ctx, const void* idx_dev, int64_t first_slot, int64_t count, const void* rows_dev,
+                              void* stream) {
+    REQUIRE_SLAB(ctx);
+    if (count <= 0) return 0;
+    if (!idx_dev && (first_slot < 0 || first_slot + count > ctx->capacity)) MPMK_FAIL(ctx, MPMK_ERR_INVALID, "mpmk_mg_unpack: beyond capacity");
+    const MgRecordPtrs P = record_ptrs(ctx);
+    k_mg_unpack<<<div_up(count * (P.n_arrays + 1), 256), 256, 0, (cudaStream_t)stream>>>(P, (uint32_t*)ctx->b.keys, (const int*)idx_dev,
+                                                                                           first_slot, count, (const int*)rows_dev);
+    MPMK_LAUNCH_CHECK(ctx);
+    return 0;
+}
+
+extern "C" int mpmk_mg_close_holes(mpmk_ctx* ctx, const void* holes_dev, int64_t n_holes, int64_t n_new, void* scratch_dev,
+                                   int64_t scratch_bytes, void* stream) {
+    REQUIRE_SLAB(ctx);
+    const int64_t tail_len = ctx->n - n_new;
+    if (n_holes <= 0 || tail_len <= 0) return 0;
+    // scratch: int counters[2] | int low_holes[n_holes] | uchar tail_flag[tail_len]
+    const int64_t need = 8 + 4 * n_holes + tail_len;
+    if (scratch_bytes < need) MPMK_FAIL(ctx, MPMK_ERR_INVALID, "mpmk_mg_close_holes: scratch %lld < %lld bytes", (long long)scratch_bytes, (long long)need);
+    cudaStream_t s = (cudaStream_t)stream;
+    int* counters = (int*)scratch_dev;
+    int* low = counters + 2;
+    unsigned char* flag = (unsigned char*)(low + n_holes);
+    MPMK_CHECK(ctx, cudaMemsetAsync(scratch_dev, 0, (size_t)need, s));
+    k_mg_split_holes<<<div_up(n_holes, 256), 256, 0, s>>>((const int*)holes_dev, n_holes, n_new, low, counters, flag);
+    MPMK_LAUNCH_CHECK(ctx);
+    const MgRecordPtrs P = record_ptrs(ctx);
+    k_mg_move_tail<<<div_up(tail_len, 256), 256, 0, s>>>(P, (uint32_t*)ctx->b.keys, n_new, tail_len, low, counters, flag);
+    MPMK_LAUNCH_CHECK(ctx);
+    return 0;
 }

@@ -27,10 +27,18 @@
 #define P2G_REC_SLOTS 12   // 9 x {Y_ij.xyz, wx_i wy_j} + 3 x {R_k.xyz, wz_k}
 
 #define P2G_NSTAGE 6       // xm, vv, c0, c1, cs, s1
+#define P2G_TILE_SX 37     // x stride of the shared tile in float4 (6*6 + 1 pad)
+#define P2G_TILE_F4 (6 * P2G_TILE_SX)
+
+// lane -> stencil node (i*9 + j*3 + k).  Shared memory serves a 16-byte access per quarter-warp, 8 float4 bank
+// groups wide: the map puts into every quarter-warp nodes whose tile slots (37 i + 6 j + k) and whose Y_ij record
+// slots (3 i + j) fall into distinct bank groups, so neither the tile read-modify-write nor the record reads
+// replay.  Lanes 27..31 mirror lane 26 (same addresses: a broadcast) and never write.
+__constant__ unsigned char P2G_LANE_NODE[32] = {2, 1, 11, 19, 9, 10, 21, 13, 24, 18, 4, 15, 5, 14, 6, 12, 3, 23, 7, 22, 25, 17, 20, 26, 8, 16, 0, 0, 0, 0, 0, 0};
 
 struct __align__(16) P2GWarpSmem {
     float4 rec[P2G_REC_SLOTS * P2G_REC_STRIDE];
-    float4 tile[MPMK_TILE_NODES];
+    float4 tile[P2G_TILE_F4];
     float4 stage[P2G_NSTAGE][32];  // next batch's particle records, in flight (cp.async) while this batch is scattered
 };
 
@@ -53,11 +61,12 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
     const int lane = threadIdx.x & 31;
     P2GWarpSmem& S = reinterpret_cast<P2GWarpSmem*>(smem_raw)[warp];
     const bool node_lane = lane < 27;
-    const int ni = node_lane ? lane / 9 : 0, nj = node_lane ? (lane / 3) % 3 : 0, nk = node_lane ? lane % 3 : 0;
+    const int node = P2G_LANE_NODE[lane];
+    const int ni = node / 9, nj = (node / 3) % 3, nk = node % 3;
     const int nij = ni * 3 + nj;
-    const int noff = ni * 36 + nj * 6 + nk;
+    const int noff = ni * P2G_TILE_SX + nj * 6 + nk;
     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int i = lane; i < MPMK_TILE_NODES; i += 32) S.tile[i] = zero4;
+    for (int i = lane; i < P2G_TILE_F4; i += 32) S.tile[i] = zero4;
     __syncwarp();
     const int n = a.n_grid;
 
@@ -193,7 +202,7 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
             while (l < nbatch) {
                 if ((heads >> l) & 1u) {
                     if (cur_cell >= 0 && node_lane) {
-                        const int nd = (cur_cell >> 4) * 36 + ((cur_cell >> 2) & 3) * 6 + (cur_cell & 3) + noff;
+                        const int nd = (cur_cell >> 4) * P2G_TILE_SX + ((cur_cell >> 2) & 3) * 6 + (cur_cell & 3) + noff;
                         float4 t = S.tile[nd];
                         t.x += acc.x; t.y += acc.y; t.z += acc.z; t.w += acc.w;
                         S.tile[nd] = t;
@@ -217,15 +226,16 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
             // end of the item: last cell run -> tile, tile -> global grid (16-byte vector reductions)
             if (dB.count == 0 || dB.first) {
                 if (cur_cell >= 0 && node_lane) {
-                    const int nd = (cur_cell >> 4) * 36 + ((cur_cell >> 2) & 3) * 6 + (cur_cell & 3) + noff;
+                    const int nd = (cur_cell >> 4) * P2G_TILE_SX + ((cur_cell >> 2) & 3) * 6 + (cur_cell & 3) + noff;
                     float4 t = S.tile[nd];
                     t.x += acc.x; t.y += acc.y; t.z += acc.z; t.w += acc.w;
                     S.tile[nd] = t;
                 }
                 __syncwarp();
                 for (int i = lane; i < MPMK_TILE_NODES; i += 32) {
-                    const float4 t = S.tile[i];
-                    S.tile[i] = zero4;
+                    const int ti = i + i / 36;  // x*37 + y*6 + z
+                    const float4 t = S.tile[ti];
+                    S.tile[ti] = zero4;
                     if (t.x != 0.f || t.y != 0.f || t.z != 0.f || t.w != 0.f) {
                         const int gx = 4 * tx + i / 36, gy = 4 * ty + (i / 6) % 6, gz = 4 * tz + i % 6;
                         if (gx < n && gy < n && gz < n) red_add_v4(a.grid_in + (((size_t)gx * n + gy) * n + gz), t);

@@ -117,6 +117,11 @@ def lib():
         "mpmk_mg_finalize": (i, [vp]),
         "mpmk_mg_set_slab": (i, [vp, i, i, i, i, i, vp, vp]),
         "mpmk_mg_halo_exchange": (i, [vp, vp]),
+        "mpmk_mg_set_count": (i, [vp, i64]),
+        "mpmk_mg_scan": (i, [vp, vp, vp, vp, vp]),
+        "mpmk_mg_pack": (i, [vp, vp, i64, vp, vp]),
+        "mpmk_mg_unpack": (i, [vp, vp, i64, i64, vp, vp]),
+        "mpmk_mg_close_holes": (i, [vp, vp, i64, i64, vp, i64, vp]),
     }
     L.mpmk_mg_unique_id.restype = i
     L.mpmk_mg_unique_id.argtypes = [C.c_char_p, vp, i]

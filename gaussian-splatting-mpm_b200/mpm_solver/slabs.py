@@ -16,10 +16,33 @@ migration protocol are exercised on CPU tensors by the world_size-2 gloo tests (
 """
 from __future__ import annotations
 
+import os
+import time
+
 import torch
 import torch.distributed as dist
 
-RECORD_ARRAYS = ("xm", "vv", "c0", "c1", "cs", "s1", "f0", "f1", "f2", "meta", "cv0", "cv1")
+_TIMING = bool(os.environ.get("MPMK_SLAB_TIMING"))
+_marks = []
+
+
+def _mark(name, device):
+    """MPMK_SLAB_TIMING=1: wall time of each migration phase (synchronising; tuning aid only)"""
+    if _TIMING:
+        if device.type == "cuda":
+            torch.cuda.synchronize(device)
+        _marks.append((name, time.perf_counter()))
+
+
+def timing_report():
+    out, acc = [], {}
+    for (a, ta), (b, tb) in zip(_marks, _marks[1:]):
+        if b != "begin":
+            acc.setdefault(b, []).append(round((tb - ta) * 1e3, 3))
+    return acc
+
+
+RECORD_ARRAYS = ("xm", "vv", "c0", "c1", "cs", "s1", "f0", "f1", "f2", "meta", "cv0", "cv1", "ft0", "ft1", "ft2")
 
 
 class SlabError(RuntimeError):
@@ -135,7 +158,94 @@ def _payload_exchange(send_lo, send_hi, n_from_lo, n_from_hi, rank, world, group
     return recv_lo, recv_hi
 
 
-def migrate(store: dict, n: int, capacity: int, bounds, rank: int, ghost: int, nt: int, n_grid: int = None, group=None):
+class TorchRecordOps:
+    """scan / pack / refill on plain torch tensors of any device (the CPU tests run this over gloo)"""
+
+    def __init__(self, store: dict, nt: int, n_grid: int):
+        self.store, self.nt, self.n_grid = store, nt, n_grid
+        self.device = store["keys"].device
+
+    def scan(self, n, x_lo, x_hi, ghost):
+        """int64[6] on the device: leavers down, leavers up, beyond ghost, -min row, max row, max(|vx|,|vy|) bits"""
+        if n == 0:
+            self.lo_mask = self.hi_mask = torch.zeros(0, dtype=torch.bool, device=self.device)
+            return torch.tensor([0, 0, 0, -self.n_grid, -1, 0], dtype=torch.int64, device=self.device)
+        bx, by = _base_xy_i32(self.store["keys"][:n], self.nt)
+        self.lo_mask, self.hi_mask = bx < x_lo, bx >= x_hi
+        far = (bx < x_lo - ghost) | (bx >= x_hi + ghost)
+        vmax = self.store["vv"][:n, :2].abs().max().reshape(1).to(torch.float32).view(torch.int32)[0]
+        return torch.stack([self.lo_mask.sum(), self.hi_mask.sum(), far.sum(), -by.min().to(torch.int64),
+                            by.max().to(torch.int64), vmax.to(torch.int64)])
+
+    def pack_leavers(self, n_lo, n_hi):
+        self.idx_lo = torch.nonzero_static(self.lo_mask, size=n_lo).flatten()
+        self.idx_hi = torch.nonzero_static(self.hi_mask, size=n_hi).flatten()
+        return pack_records(self.store, self.idx_lo), pack_records(self.store, self.idx_hi)
+
+    def refill(self, n, n_new, arrivals):
+        store, device = self.store, self.device
+        holes = torch.cat([self.idx_lo, self.idx_hi])
+        free = [holes[holes < n_new]]
+        rows_in = [arrivals]
+        if n_new > n:
+            free.append(torch.arange(n, n_new, device=device))
+        elif n_new < n:
+            tail_is_hole = torch.zeros(n - n_new, dtype=torch.bool, device=device)
+            tail_is_hole[holes[holes >= n_new] - n_new] = True
+            live_tail = torch.nonzero(~tail_is_hole).flatten() + n_new
+            rows_in.append(pack_records(store, live_tail))
+        free = torch.cat(free)
+        rows_in = torch.cat(rows_in)
+        if free.numel() != rows_in.shape[0]:
+            raise SlabError(f"migration bookkeeping mismatch ({free.numel()} free slots, {rows_in.shape[0]} records)")
+        if free.numel():
+            unpack_records(store, free, rows_in)
+
+
+class CudaRecordOps:
+    """the same three steps as kernels of libmpmk (csrc/mg.cu) on the simulator's packed arrays: one pass for the
+    scan, one launch each to pack / unpack, two to close the holes of a shrinking slab; no host synchronisation"""
+
+    def __init__(self, backend, stream_fn):
+        self.b, self._stream = backend, stream_fn
+        dev = backend.device
+        self.device = dev
+        self.stats = torch.zeros(8, dtype=torch.int32, device=dev)
+        self.idx_lo = torch.zeros(backend.capacity, dtype=torch.int32, device=dev)
+        self.idx_hi = torch.zeros(backend.capacity, dtype=torch.int32, device=dev)
+
+    def scan(self, n, x_lo, x_hi, ghost):
+        self.b.ctx.call("mpmk_mg_scan", self.stats.data_ptr(), self.idx_lo.data_ptr(), self.idx_hi.data_ptr(), self._stream())
+        return self.stats[:6].to(torch.int64)
+
+    def pack_leavers(self, n_lo, n_hi):
+        self.n_lo, self.n_hi = n_lo, n_hi
+        out = []
+        for idx, cnt in ((self.idx_lo, n_lo), (self.idx_hi, n_hi)):
+            rows = torch.empty((cnt, RECORD_WIDTH), dtype=torch.int32, device=self.device)
+            self.b.ctx.call("mpmk_mg_pack", idx.data_ptr(), cnt, rows.data_ptr(), self._stream())
+            out.append(rows)
+        return out
+
+    def refill(self, n, n_new, arrivals):
+        call, st = self.b.ctx.call, self._stream()
+        L, R = self.n_lo + self.n_hi, int(arrivals.shape[0])
+        holes = torch.cat([self.idx_lo[: self.n_lo], self.idx_hi[: self.n_hi]])
+        arrivals = arrivals.contiguous()
+        k = min(L, R)
+        if k:
+            call("mpmk_mg_unpack", holes.data_ptr(), 0, k, arrivals.data_ptr(), st)
+        if R > L:     # the rest is appended at [n, n_new)
+            call("mpmk_mg_unpack", None, n, R - L, arrivals[L:].contiguous().data_ptr(), st)
+        elif L > R:   # the slab shrinks: live records of the tail move into the unfilled holes below n_new
+            rest = holes[R:].contiguous()
+            nbytes = 8 + 4 * (L - R) + (n - n_new)
+            scratch = torch.empty(nbytes + 16, dtype=torch.uint8, device=self.device)
+            call("mpmk_mg_close_holes", rest.data_ptr(), L - R, n_new, scratch.data_ptr(), nbytes, st)
+
+
+def migrate(store: dict, n: int, capacity: int, bounds, rank: int, ghost: int, nt: int, n_grid: int = None, group=None,
+            ops=None):
     """Move the particles whose base-cell plane left [bounds[rank], bounds[rank+1]) to the neighbouring
     rank and take in what the neighbours send.  `store` maps the packed array names (+ "keys") to tensors
     of `capacity` records whose first `n` are live.  Holes left by leavers are refilled by arrivals and,
@@ -143,27 +253,26 @@ def migrate(store: dict, n: int, capacity: int, bounds, rank: int, ghost: int, n
     (their order is irrelevant: every substep starts with a sort).
 
     One collective and one host synchronisation: every rank contributes {leavers down, leavers up, particles
-    beyond the ghost margin, -min row, max row} to an all_gather, from which each rank reads its neighbours'
-    counts, the global error flag and the global row range.  Returns (n_new, stats)."""
+    beyond the ghost margin, -min row, max row, max speed} to an all_gather, from which each rank reads its
+    neighbours' counts, the global error flag, the global row range and the global speed bound.
+    `ops` does the data movement (TorchRecordOps by default, CudaRecordOps on the simulator's arrays).
+    Returns (n_new, stats)."""
     world = len(bounds) - 1
     x_lo, x_hi = bounds[rank], bounds[rank + 1]
     device = store["keys"].device
     n_grid = n_grid if n_grid is not None else 4 * nt
-    keys = store["keys"][:n]
-    if n > 0:
-        bx, by = _base_xy_i32(keys, nt)
-        lo_mask, hi_mask = bx < x_lo, bx >= x_hi
-        far = (bx < x_lo - ghost) | (bx >= x_hi + ghost)
-        mine = torch.stack([lo_mask.sum(), hi_mask.sum(), far.sum(), -by.min().to(torch.int64), by.max().to(torch.int64)])
-    else:
-        lo_mask = hi_mask = torch.zeros(0, dtype=torch.bool, device=device)
-        mine = torch.tensor([0, 0, 0, -n_grid, -1], dtype=torch.int64, device=device)
-    table = torch.empty(world * 5, dtype=torch.int64, device=device)
+    if ops is None:
+        ops = TorchRecordOps(store, nt, n_grid)
+    _mark("begin", device)
+    mine = ops.scan(n, x_lo, x_hi, ghost)
+    table = torch.empty(world * 6, dtype=torch.int64, device=device)
     if world > 1:
-        dist.all_gather_into_tensor(table, mine.to(torch.int64).contiguous(), group=group)
+        dist.all_gather_into_tensor(table, mine.contiguous(), group=group)
     else:
-        table[:5] = mine
-    table = table.view(world, 5).cpu()                    # the one synchronisation
+        table[:6] = mine
+    _mark("scan", device)
+    table = table.view(world, 6).cpu()                    # the one synchronisation
+    _mark("allgather+sync", device)
     if int(table[:, 2].sum()):
         bad = [r for r in range(world) if int(table[r, 2])]
         raise SlabError(f"ranks {bad}: particles drifted more than ghost={ghost} planes outside their slab between "
@@ -173,33 +282,19 @@ def migrate(store: dict, n: int, capacity: int, bounds, rank: int, ghost: int, n
     n_from_hi = int(table[rank + 1, 0]) if rank < world - 1 else 0
     y_min, y_max = -int(table[:, 3].max()), int(table[:, 4].max())
     rows = (0, n_grid) if y_max < y_min else (max(0, y_min - ghost - 1), min(n_grid, y_max + 3 + ghost + 1))
-    stats = {"sent_lo": n_lo, "sent_hi": n_hi, "recv_lo": n_from_lo, "recv_hi": n_from_hi, "rows": rows}
+    vmax = float(table[:, 5].max().to(torch.int32).reshape(1).view(torch.float32)[0])
+    stats = {"sent_lo": n_lo, "sent_hi": n_hi, "recv_lo": n_from_lo, "recv_hi": n_from_hi, "rows": rows, "vmax": vmax}
     if n_lo + n_hi + n_from_lo + n_from_hi == 0:
         return n, stats
-    idx_lo = torch.nonzero_static(lo_mask, size=n_lo).flatten()
-    idx_hi = torch.nonzero_static(hi_mask, size=n_hi).flatten()
-    recv_lo, recv_hi = _payload_exchange(pack_records(store, idx_lo), pack_records(store, idx_hi), n_from_lo, n_from_hi,
-                                         rank, world, group, device)
-    holes = torch.cat([idx_lo, idx_hi])
-    arrivals = torch.cat([recv_lo, recv_hi])
-    n_new = n - holes.numel() + arrivals.shape[0]
+    n_new = n - n_lo - n_hi + n_from_lo + n_from_hi
     if n_new > capacity:
         raise SlabError(f"rank {rank}: {n_new} particles after migration exceed the capacity {capacity}")
-    free = [holes[holes < n_new]]
-    rows_in = [arrivals]
-    if n_new > n:
-        free.append(torch.arange(n, n_new, device=device))
-    elif n_new < n:
-        tail_is_hole = torch.zeros(n - n_new, dtype=torch.bool, device=device)
-        tail_is_hole[holes[holes >= n_new] - n_new] = True
-        live_tail = torch.nonzero(~tail_is_hole).flatten() + n_new
-        rows_in.append(pack_records(store, live_tail))
-    free = torch.cat(free)
-    rows_in = torch.cat(rows_in)
-    if free.numel() != rows_in.shape[0]:
-        raise SlabError(f"rank {rank}: migration bookkeeping mismatch ({free.numel()} free slots, {rows_in.shape[0]} records)")
-    if free.numel():
-        unpack_records(store, free, rows_in)
+    send_lo, send_hi = ops.pack_leavers(n_lo, n_hi)
+    _mark("pack", device)
+    recv_lo, recv_hi = _payload_exchange(send_lo, send_hi, n_from_lo, n_from_hi, rank, world, group, device)
+    _mark("p2p", device)
+    ops.refill(n, n_new, torch.cat([recv_lo, recv_hi]))
+    _mark("refill", device)
     return n_new, stats
 
 
@@ -246,7 +341,7 @@ class SlabSimulator:
             raise SlabError("bounds must hold world+1 cuts")
         self.ghost = int(ghost)
         check_bounds(self.bounds, self.ghost)
-        self.migrate_every = int(migrate_every)
+        self.migrate_every = int(migrate_every) if migrate_every not in (None, 0, "auto") else 0
         self.n_global = int(n_global)
         n = int(xyz.shape[0])
         cap = int(capacity if capacity is not None else max(int(1.25 * n) + 4096, 8192))
@@ -279,9 +374,16 @@ class SlabSimulator:
         z = lambda: torch.zeros((planes * self.n_grid * self.n_grid, 4), dtype=torch.float32, device=self.device)
         self._recv_lo = z() if self.rank > 0 else None
         self._recv_hi = z() if self.rank < self.world - 1 else None
+        self._ops = CudaRecordOps(b, _stream)
+        self._auto = migrate_every in (None, 0, "auto")
+        self.max_interval = 64
+        self._dt = float(args.substep_dt)
+        if self._auto:
+            self.migrate_every = 1   # until the first migration has measured the speeds
         self.stats = {"migrations": 0, "sent": 0, "received": 0}
         self._since_migration = 0
         self._replicate_init_cov()
+        self._warm_up_p2p()
         self._set_slab()
 
     # -- plumbing ---------------------------------------------------------------------------------
@@ -292,8 +394,25 @@ class SlabSimulator:
     def _store(self):
         b = self.backend
         st = dict(b.cur)
+        st["ft0"], st["ft1"], st["ft2"] = b.ft   # F_trial of the last substep travels with the particle (export)
         st["keys"] = b.keys
         return st
+
+    def _warm_up_p2p(self):
+        """one dummy record each way now, so that the first real migration does not pay for setting up the
+        point-to-point connections (~0.1 s with NCCL)"""
+        dummy = torch.zeros((1, RECORD_WIDTH), dtype=torch.int32, device=self.device)
+        n_lo = 1 if self.rank > 0 else 0
+        n_hi = 1 if self.rank < self.world - 1 else 0
+        _payload_exchange(dummy[:n_lo], dummy[:n_hi], n_lo, n_hi, self.rank, self.world, self.group, self.device)
+
+    def _choose_interval(self, vmax):
+        """migrate_every="auto": as many substeps as the fastest particle needs to cross half the ghost margin"""
+        if not self._auto:
+            return
+        dx = self.sim.mpm_model.dx
+        per_substep = max(vmax * self._dt / dx, 1e-9)
+        self.migrate_every = int(max(1, min(self.max_interval, 0.5 * self.ghost / per_substep)))
 
     def _replicate_init_cov(self):
         """export needs Sigma_0 of whatever particle a rank holds after migrations: every rank wrote the rows
@@ -310,16 +429,20 @@ class SlabSimulator:
 
     def migrate(self):
         b = self.backend
-        n_new, st = migrate(self._store(), b.n, b.capacity, self.bounds, self.rank, self.ghost, self.nt, self.n_grid, self.group)
+        _mark("begin", self.device)
+        n_new, st = migrate(self._store(), b.n, b.capacity, self.bounds, self.rank, self.ghost, self.nt, self.n_grid, self.group,
+                            ops=self._ops)
         b.n = n_new
         self.sim.n_particles = n_new
-        b.ctx.call("mpmk_set_count", n_new, b.ctx.L.mpmk_current_set(b.ctx.h))
+        b.ctx.call("mpmk_mg_set_count", n_new)
         b.invalidate()
         self.stats["migrations"] += 1
         self.stats["sent"] += st["sent_lo"] + st["sent_hi"]
         self.stats["received"] += st["recv_lo"] + st["recv_hi"]
         self._since_migration = 0
+        self._choose_interval(st["vmax"])
         self._set_slab(st["rows"])
+        _mark("set_slab", self.device)
         return st
 
     def reload(self, xyz, cov, vol, vel, ids):
@@ -349,6 +472,8 @@ class SlabSimulator:
         done = 0
         while done < n_substeps:
             k = min(n_substeps - done, self.migrate_every - self._since_migration)
+            if dt is not None:
+                self._dt = float(dt)
             self.sim.step(k, dt)
             done += k
             self._since_migration += k

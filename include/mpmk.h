@@ -193,7 +193,7 @@ MPMK_API int mpmk_export(mpmk_ctx* ctx, const void* init_cov_dev, void* xyz_out_
  * cells outside.  After p2g the partial sums on the planes shared with each
  * neighbour are exchanged (ncclSend/ncclRecv on the caller's stream) and added
  * symmetrically, after which both neighbours run the grid update on them.
- * Particle migration is host-orchestrated (harness/slabs.py) between batches.  */
+ * Particle migration is host-orchestrated (mpm_solver/slabs.py) between batches.  */
 /* rank 0: create the 128-byte NCCL unique id that the host layer broadcasts     */
 MPMK_API int mpmk_mg_unique_id(const char* nccl_lib_path, void* id_out, int id_bytes);
 /* all ranks: join the communicator (nccl_lib_path: the libnccl.so.2 torch loaded) */
@@ -205,6 +205,24 @@ MPMK_API int mpmk_mg_finalize(mpmk_ctx* ctx);
  * outer ranks); from here on mpmk_substep/mpmk_substeps include the halo sum      */
 MPMK_API int mpmk_mg_set_slab(mpmk_ctx* ctx, int x_lo, int x_hi, int ghost, int y_lo, int y_hi, void* recv_lo_dev,
                               void* recv_hi_dev);
+/* new live particle count after a host-side migration (mpm_solver/slabs.py); unlike mpmk_set_count
+ * it keeps the current set and the validity of the stored F_trial records                       */
+MPMK_API int mpmk_mg_set_count(mpmk_ctx* ctx, int64_t n_particles);
+/* Migration helpers; the protocol is mpm_solver/slabs.py.  A record = the 16-byte entries of the 12 set arrays
+ * and ft0..ft2 (15 x 4 words) + the key = 61 x int32.
+ * scan: one pass over the live keys; stats_dev int32[8] = {leavers to rank-1, leavers to rank+1, particles more
+ * than `ghost` planes outside the slab, -(min base row), max base row, max(|v_x|,|v_y|) (float bits), 0, 0};
+ * idx_lo_dev / idx_hi_dev int32[capacity] receive the slots of the leavers (unordered).                      */
+MPMK_API int mpmk_mg_scan(mpmk_ctx* ctx, void* stats_dev, void* idx_lo_dev, void* idx_hi_dev, void* stream);
+/* rows_dev int32[count][61] <- records at slots idx_dev[0..count)                                          */
+MPMK_API int mpmk_mg_pack(mpmk_ctx* ctx, const void* idx_dev, int64_t count, void* rows_dev, void* stream);
+/* records at slots idx_dev[r] (or first_slot + r when idx_dev is NULL) <- rows_dev[r]                        */
+MPMK_API int mpmk_mg_unpack(mpmk_ctx* ctx, const void* idx_dev, int64_t first_slot, int64_t count, const void* rows_dev,
+                            void* stream);
+/* the slab shrinks to n_new < n: move the live records of [n_new, n) into the n_holes unfilled leaver slots
+ * (holes_dev) that lie below n_new; scratch_dev: 8 + 4*n_holes + (n - n_new) bytes                           */
+MPMK_API int mpmk_mg_close_holes(mpmk_ctx* ctx, const void* holes_dev, int64_t n_holes, int64_t n_new, void* scratch_dev,
+                                 int64_t scratch_bytes, void* stream);
 /* the halo sum alone (stagewise use: after mpmk_p2g, before mpmk_grid_update)     */
 MPMK_API int mpmk_mg_halo_exchange(mpmk_ctx* ctx, void* stream);
 

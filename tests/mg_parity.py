@@ -22,7 +22,7 @@ from mpm_solver.solver import MPM_Simulator  # noqa: E402
 TOL_X, TOL_F = 1e-4, 1e-4   # max|dx| / grid dx ; relative Frobenius error of cov (F Sigma0 F^T)
 
 
-def run_case(material, S, rank, world, dev, omega):
+def run_case(material, S, rank, world, dev, omega, ghost=1, migrate_every=5):
     n_grid, lo, cn, dt = 64, (22, 22, 22), (20, 20, 20), 4e-4
     cloud = synthetic.make_cloud(n_grid, 2.0, lo, cn, seed=5, omega=omega)
     args = synthetic.sim_args(n_grid=n_grid, material=material, substep_dt=dt)
@@ -32,12 +32,14 @@ def run_case(material, S, rank, world, dev, omega):
     part, ids = slabs.partition_cloud(cloud, bounds, rank, args.n_grid / args.grid_extent, n_grid)
     t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
     sl = slabs.SlabSimulator(t(part["xyz"]), t(part["cov"]), t(part["vol"]), args, t(ids), N, bounds, vel=t(part["vel"]),
-                             ghost=1, migrate_every=5, boundary_conditions=ops["boundary_conditions"],
+                             ghost=ghost, migrate_every=migrate_every, boundary_conditions=ops["boundary_conditions"],
                              collider=ops["collider"], strict_q1=False)
     assert sl.global_count() == N
     sl.step(S, dt)
     assert sl.global_count() == N, "particles were lost or duplicated in migration"
     # ownership: every particle sits on the rank owning its base-cell plane right after a migration
+    if sl._since_migration:
+        sl.migrate()
     gid, _, _, _ = sl.gather()
     bx, _, _ = slabs.key_base_xyz(sl.backend.keys[: sl.n_particles], sl.nt)
     assert bool(((bx >= bounds[rank]) & (bx < bounds[rank + 1])).all())
@@ -88,8 +90,9 @@ def main():
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     ok = True
-    for material, S, omega in (("jelly", 40, (0.0, 0.0, 20.0)), ("sand", 20, (0.0, 0.0, 20.0))):
-        ok = run_case(material, S, rank, world, dev, omega) and ok
+    for material, S, omega, ghost, every in (("jelly", 40, (0.0, 0.0, 20.0), 1, 5), ("sand", 20, (0.0, 0.0, 20.0), 1, 5),
+                                             ("metal", 30, (0.0, 0.0, 20.0), 2, "auto")):
+        ok = run_case(material, S, rank, world, dev, omega, ghost, every) and ok
     dist.barrier()
     if rank == 0:
         print("mg parity ok" if ok else "mg parity FAILED", flush=True)
