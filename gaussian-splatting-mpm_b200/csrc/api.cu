@@ -35,8 +35,8 @@ static int create_impl(mpmk_ctx* ctx, int device, int n_grid, double grid_extent
     ALLOC0(ctx, ctx->perm, cap * 4);
     ALLOC0(ctx, ctx->perm_alt, cap * 4);
     ctx->n_sort_ctas_cap = div_up((int64_t)cap, MPMK_SORT_CHUNK);
-    ALLOC0(ctx, ctx->hist, (size_t)(1 << MPMK_MAX_RADIX_BITS) * ctx->n_sort_ctas_cap * 4);
-    ALLOC0(ctx, ctx->hist_tot, 1024 * 4);
+    ALLOC0(ctx, ctx->sort_ctrl, ((size_t)8 + 4 * 512 + (size_t)4 * (1 << MPMK_MAX_RADIX_BITS) * ctx->n_sort_ctas_cap) * 4);
+    ALLOC0(ctx, ctx->hist_tot, 4 * 512 * 4);
     const size_t ntiles = (size_t)ctx->nt * ctx->nt * ctx->nt;
     ctx->items_cap = (int64_t)(cap / MPMK_ITEM_MAX + (cap < ntiles ? cap : ntiles) + 8);
     ALLOC0(ctx, ctx->items, (size_t)ctx->items_cap * sizeof(uint4));
@@ -70,7 +70,7 @@ extern "C" int mpmk_destroy(mpmk_ctx* ctx) {
     mpmk_mg_finalize(ctx);
     for (int i = 0; i < ctx->n_graphs; ++i) cudaGraphExecDestroy(ctx->graphs[i].exec);
     cudaFree(ctx->keys_alt); cudaFree(ctx->sorted_keys); cudaFree(ctx->perm); cudaFree(ctx->perm_alt);
-    cudaFree(ctx->hist); cudaFree(ctx->hist_tot); cudaFree(ctx->items); cudaFree(ctx->tile_list); cudaFree(ctx->tile_end); cudaFree(ctx->block_stamp);
+    cudaFree(ctx->sort_ctrl); cudaFree(ctx->hist_tot); cudaFree(ctx->items); cudaFree(ctx->tile_list); cudaFree(ctx->tile_end); cudaFree(ctx->block_stamp);
     cudaFree(ctx->block_list[0]); cudaFree(ctx->block_list[1]); cudaFree(ctx->block_count[0]); cudaFree(ctx->block_count[1]);
     cudaFree(ctx->counters); cudaFree(ctx->dev_stamp);
     if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);

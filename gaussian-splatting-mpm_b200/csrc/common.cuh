@@ -60,8 +60,8 @@ struct mpmk_ctx {
     uint32_t* sorted_keys;   // result of last sort
     uint32_t* perm;          // result of last sort: physical slot of the r-th particle in sorted order
     uint32_t* perm_alt;
-    uint32_t* hist;          // [digits][n_sort_ctas]
-    uint32_t* hist_tot;      // [digits]
+    uint32_t* sort_ctrl;     // one-sweep control block: tile counters, digit histograms, status words (sort.cu)
+    uint32_t* hist_tot;      // [passes][512] exclusive digit bases
     int64_t n_sort_ctas_cap;
     uint4* items;            // {begin, count, tile, 0}
     uint2* tile_list;        // non-empty tiles of the current sort: {tile, first sorted index}
