@@ -13,8 +13,12 @@
 #ifndef MPMK_ITEM_MAX
 #define MPMK_ITEM_MAX 256           // particles per p2g/g2p work item (tile chunk)
 #endif
+#ifndef MPMK_SORT_CTA
 #define MPMK_SORT_CTA 256           // threads per sort CTA
+#endif
+#ifndef MPMK_SORT_ROUNDS
 #define MPMK_SORT_ROUNDS 16         // keys per thread per sort CTA
+#endif
 #define MPMK_SORT_CHUNK (MPMK_SORT_CTA * MPMK_SORT_ROUNDS)
 #define MPMK_MAX_RADIX_BITS 9
 

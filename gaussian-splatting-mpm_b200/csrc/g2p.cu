@@ -51,11 +51,13 @@ __device__ __forceinline__ void bspline(float f, float* w, float* dw) {
 //     batch B: particle records xm,f0,f1,f2,meta in flight (cp.async, 16 B per lane per array, into
 //              the other half of a double-buffered shared-memory stage)
 //     batch A: gather + C/F update + constitutive update + stores
+// 4 warps x 5 CTAs per SM: 20 warps at <= 102 registers each.  Measured on S-4M (jelly): 8x3 (cap 85, spills)
+// 0.288 ms, 4x6 (cap 85) 0.291, 4x4 (cap 128) 0.305, 2x9 0.262, 4x5 = 2x10 0.221.
 #ifndef G2P_WARPS
-#define G2P_WARPS 8
+#define G2P_WARPS 4
 #endif
 #ifndef G2P_MIN_CTAS
-#define G2P_MIN_CTAS 3
+#define G2P_MIN_CTAS 5
 #endif
 #define G2P_NREC 5
 
