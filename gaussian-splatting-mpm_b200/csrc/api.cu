@@ -38,7 +38,7 @@ static int create_impl(mpmk_ctx* ctx, int device, int n_grid, double grid_extent
     ALLOC0(ctx, ctx->sort_ctrl, ((size_t)8 + 4 * 512 + (size_t)4 * (1 << MPMK_MAX_RADIX_BITS) * ctx->n_sort_ctas_cap) * 4);
     ALLOC0(ctx, ctx->hist_tot, 4 * 512 * 4);
     const size_t ntiles = (size_t)ctx->nt * ctx->nt * ctx->nt;
-    ctx->items_cap = (int64_t)(cap / MPMK_ITEM_MAX + (cap < ntiles ? cap : ntiles) + 8);
+    ctx->items_cap = (int64_t)(cap / MPMK_ITEM_MIN + (cap < ntiles ? cap : ntiles) + 8);
     ALLOC0(ctx, ctx->items, (size_t)ctx->items_cap * sizeof(uint4));
     ALLOC0(ctx, ctx->tile_list, ((cap < ntiles ? cap : ntiles) + 8) * sizeof(uint2));
     ALLOC0(ctx, ctx->tile_end, ntiles * 4);

@@ -13,6 +13,7 @@
 #ifndef MPMK_ITEM_MAX
 #define MPMK_ITEM_MAX 256           // particles per p2g/g2p work item (tile chunk)
 #endif
+#define MPMK_ITEM_MIN 32            // smallest work item (one batch)
 #ifndef MPMK_SORT_CTA
 #define MPMK_SORT_CTA 256           // threads per sort CTA
 #endif
@@ -200,6 +201,7 @@ struct BatchStream {
 int mpmk_launch_keys(mpmk_ctx* ctx, cudaStream_t s);
 int mpmk_launch_sort(mpmk_ctx* ctx, cudaStream_t s);
 int mpmk_launch_prepare(mpmk_ctx* ctx, cudaStream_t s);
+int mpmk_item_size(const mpmk_ctx* ctx);
 int mpmk_launch_p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);
 int mpmk_launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);
 int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s);

@@ -49,18 +49,18 @@ __global__ void __launch_bounds__(256) k_tile_runs(const uint32_t* __restrict__ 
 __global__ void __launch_bounds__(256) k_build_items(const uint2* __restrict__ tile_list, const uint32_t* __restrict__ tile_end,
                                                      uint4* __restrict__ items, DevCounters* cnt, uint32_t* __restrict__ stamp_arr,
                                                      const uint32_t* __restrict__ stamp_ptr, uint32_t* __restrict__ blist,
-                                                     uint32_t* __restrict__ bcount, int nt, int nb) {
+                                                     uint32_t* __restrict__ bcount, int nt, int nb, uint32_t item_max) {
     const uint32_t n_tiles = cnt->n_tiles;
     const uint32_t stamp = *stamp_ptr;
     for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n_tiles; t += gridDim.x * blockDim.x) {
         const uint2 tl = tile_list[t];
         const uint32_t tile = tl.x, r = tl.y;
         const uint32_t np = tile_end[tile] - r;
-        const uint32_t ni = (np + MPMK_ITEM_MAX - 1) / MPMK_ITEM_MAX;
+        const uint32_t ni = (np + item_max - 1) / item_max;
         const uint32_t base = atomicAdd(&cnt->n_items, ni);
         for (uint32_t j = 0; j < ni; ++j) {
-            const uint32_t b0 = j * MPMK_ITEM_MAX;
-            items[base + j] = make_uint4(r + b0, min((uint32_t)MPMK_ITEM_MAX, np - b0), tile, 0u);
+            const uint32_t b0 = j * item_max;
+            items[base + j] = make_uint4(r + b0, min(item_max, np - b0), tile, 0u);
         }
         const int tz = tile % nt, ty = (tile / nt) % nt, tx = tile / (nt * nt);
 #pragma unroll
@@ -72,6 +72,19 @@ __global__ void __launch_bounds__(256) k_build_items(const uint2* __restrict__ t
             }
         }
     }
+}
+
+// Particles per work item: MPMK_ITEM_MAX when that still yields a few items per resident warp, else smaller
+// (a multiple of the 32-particle batch) so that small scenes -- a few hundred tiles holding hundreds of particles
+// per cell, like the reference's 50^3 configs -- still spread over all SMs.
+int mpmk_item_size(const mpmk_ctx* ctx) {
+    const int64_t warps = (int64_t)ctx->sm_count * ctx->g2p_ctas_per_sm * 4;  // resident g2p warps (the larger grid)
+    const int64_t want_items = 4 * warps;
+    int64_t sz = MPMK_ITEM_MAX;
+    if (ctx->n / MPMK_ITEM_MAX < want_items) sz = ((ctx->n / want_items + 31) / 32) * 32;
+    if (sz < MPMK_ITEM_MIN) sz = MPMK_ITEM_MIN;
+    if (sz > MPMK_ITEM_MAX) sz = MPMK_ITEM_MAX;
+    return (int)sz;
 }
 
 int mpmk_launch_prepare(mpmk_ctx* ctx, cudaStream_t s) {
@@ -89,7 +102,7 @@ int mpmk_launch_prepare(mpmk_ctx* ctx, cudaStream_t s) {
         MPMK_LAUNCH_CHECK(ctx);
         k_build_items<<<ctx->sm_count, 256, 0, s>>>(ctx->tile_list, ctx->tile_end, ctx->items, ctx->counters, ctx->block_stamp,
                                                     ctx->dev_stamp, ctx->block_list[next], ctx->block_count[next], ctx->nt,
-                                                    ctx->nb);
+                                                    ctx->nb, (uint32_t)mpmk_item_size(ctx));
         MPMK_LAUNCH_CHECK(ctx);
     }
     ctx->cur_list = next;

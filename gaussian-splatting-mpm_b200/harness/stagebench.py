@@ -26,9 +26,14 @@ def main():
     from harness import synthetic
     from mpm_solver.solver import MPM_Simulator
     dev = torch.device("cuda", 0)
-    cloud, args, ops = synthetic.workload(a.workload)
-    args.material = a.material
     t = lambda x: torch.from_numpy(x).to(dev)
+    if a.workload in synthetic.CONFIG_SHAPES:
+        from internel_filling.filling import get_particle_volume
+        cloud, args, ops = synthetic.config_workload(a.workload)
+        cloud["vol"] = get_particle_volume(t(cloud["xyz"]), args).cpu().numpy()   # main.py:270
+    else:
+        cloud, args, ops = synthetic.workload(a.workload)
+        args.material = a.material
     sim = MPM_Simulator(t(cloud["xyz"]), t(cloud["cov"]), t(cloud["vol"]), args, strict_q1=a.strict_q1)
     sim.set_boundary_conditions(ops["boundary_conditions"], args)
     sim.add_surface_collider(ops["collider"]["point"], ops["collider"]["normal"], friction=ops["collider"]["friction"])
@@ -62,7 +67,7 @@ def main():
     for r in range(a.reps):
         for i, k in enumerate(stages):
             acc[k] += evs[r][i].elapsed_time(evs[r][i + 1]) / a.reps
-    out = {"tag": a.tag, "workload": a.workload, "material": a.material, "n": n, "graph_ms_per_substep": round(graph_ms, 4),
+    out = {"tag": a.tag, "workload": a.workload, "material": args.material, "n": n, "graph_ms_per_substep": round(graph_ms, 4),
            "Gpss": round(n / graph_ms / 1e6, 3), "stage_ms": {k: round(v, 4) for k, v in acc.items()},
            "counters": sim.counters(), "finite": bool(torch.isfinite(sim.export()[0]).all())}
     print(json.dumps(out), flush=True)

@@ -87,3 +87,67 @@ def block_ops(n_grid, grid_extent, cells_lo, cells_n):
             "size": [grid_extent, grid_extent, 2 * dx], "start_time": 0.0, "num_dt": 10 ** 12}]
     collider = {"point": (0.0, 0.0, z0 - 1.0 * dx), "normal": (0.0, 0.0, 1.0), "friction": 0.0}
     return {"boundary_conditions": bcs, "collider": collider}
+
+
+# ---- config-shaped clouds --------------------------------------------------------------
+# The reference's scenes are git-LFS pointers (no .ply payload in the tree), so the named configs are
+# reproduced by SHAPE: particle count, grid, dt, material, gravity and the boundary-condition list of the
+# JSON file, with positions drawn as a Gaussian-mixture blob inside the sim-space box world2grid maps
+# scenes to ([0.5, 1.5] of the [0, 2] grid, utils/transform_utils.py:8-15).
+CONFIG_SHAPES = {
+    # configs/lego.json:9-50 (N from the LFS pointer size / 248 B)
+    "lego-like": dict(n=240_549, n_grid=50, material="jelly", E=2e5, nu=0.2, density=200.0, gravity=(0.0, 0.0, -100.0),
+                      substep_dt=1e-4, frame_dt=1e-2, bcs=[
+                          {"id": 0, "type": "fixed_cube", "center": [1.0, 1.2, 0.5], "size": [1.0, 0.8, 0.3], "start_time": 0, "num_dt": 10 ** 12},
+                          {"id": 3, "type": "fixed_cube", "center": [0.0, 1.0, 1.0], "size": [0.1, 2.0, 2.0], "start_time": 0, "num_dt": 1},
+                          {"id": 2, "type": "impulse", "center": [1.0, 0.65, 1.22], "size": [1.4, 0.18, 0.27], "force": [-0.8, 0.0, 0.0],
+                           "start_time": 0.8, "num_dt": 10}]),
+    # configs/cake_fracture_vertical.json
+    "cake-like": dict(n=669_340, n_grid=50, material="plasticine", E=7000.0, nu=0.1, density=100.0, gravity=(0.0, -320.0, 0.0),
+                      substep_dt=1e-4, frame_dt=1e-3, bcs=[
+                          {"id": 0, "type": "fixed_cube", "center": [1.0, 1.4, 1.0], "size": [1.0, 0.2, 1.0], "start_time": 0, "num_dt": 10 ** 13},
+                          {"id": 1, "type": "fixed_cube", "center": [1.0, 0.0, 1.0], "size": [1.0, 0.2, 1.0], "start_time": 0, "num_dt": 10 ** 13}]),
+    # configs/metal_cupnoodle.json (N unknown: the .ply is a missing blob; 1 M assumed)
+    "cupnoodle-like": dict(n=1_000_000, n_grid=100, material="metal", E=2e5, nu=0.4, density=500.0, gravity=(0.0, 20.0, 0.0),
+                           substep_dt=1e-4, frame_dt=1e-2, bcs=[
+                               {"id": 0, "type": "fixed_cube", "center": [2.0, 1.0, 1.0], "size": [0.4, 2.0, 2.0], "start_time": 0, "num_dt": 1},
+                               {"id": 1, "type": "impulse", "center": [1.0, 1.5, 1.0], "size": [0.8, 0.8, 0.8], "force": [0.0, 0.003, 0.0],
+                                "start_time": 0, "num_dt": 10 ** 16},
+                               {"id": 4, "type": "fixed_cube", "center": [0.0, 1.0, 1.0], "size": [0.4, 2.0, 2.0], "start_time": 0, "num_dt": 1},
+                               {"id": 5, "type": "fixed_cube", "center": [1.0, 2.0, 1.0], "size": [2.0, 0.4, 2.0], "start_time": 0, "num_dt": 1},
+                               {"id": 6, "type": "fixed_cube", "center": [1.0, 0.0, 1.0], "size": [2.0, 0.4, 2.0], "start_time": 0, "num_dt": 1},
+                               {"id": 7, "type": "fixed_cube", "center": [1.0, 1.0, 2.0], "size": [2.0, 2.0, 0.4], "start_time": 0, "num_dt": 1},
+                               {"id": 8, "type": "fixed_cube", "center": [1.0, 1.0, 0.0], "size": [2.0, 2.0, 0.4], "start_time": 0, "num_dt": 1}]),
+    # configs/bicycle.json (upper bound of N: every Gaussian of the scene inside sim_area)
+    "bicycle-like": dict(n=3_616_103, n_grid=50, material="jelly", E=2e5, nu=0.4, density=100.0, gravity=(0.0, 0.0, -3.0),
+                         substep_dt=1e-4, frame_dt=1e-2, bcs=[]),
+}
+
+
+def make_blob(n, n_grid, grid_extent=2.0, seed=SEED, n_components=24):
+    """n particles as a Gaussian mixture inside [0.55, 1.45]^3 (x,y) x [0.6, 1.45] (z) of the [0, 2] grid: dense
+    cells, hundreds of particles per cell at n_grid = 50 as in the named scenes; at rest; small random covariances"""
+    rng = np.random.default_rng(seed)
+    centres = rng.uniform(0.7, 1.3, (n_components, 3))
+    sig = rng.uniform(0.04, 0.12, (n_components, 1))
+    comp = rng.integers(0, n_components, n)
+    xyz = centres[comp] + sig[comp] * rng.standard_normal((n, 3))
+    xyz[:, :2] = np.clip(xyz[:, :2], 0.55, 1.45)
+    xyz[:, 2] = np.clip(xyz[:, 2], 0.6, 1.45)
+    dx = grid_extent / n_grid
+    s2 = (rng.uniform(0.02, 0.2, (n, 3)) * dx) ** 2
+    cov = np.stack([s2[:, 0], np.zeros(n), np.zeros(n), s2[:, 1], np.zeros(n), s2[:, 2]], 1)
+    f = lambda x: np.ascontiguousarray(x, dtype=np.float32)
+    return {"xyz": f(xyz), "vel": f(np.zeros((n, 3))), "cov": f(cov)}
+
+
+def config_workload(name, seed=SEED):
+    """(cloud without volumes, sim_args, ops) of a config-shaped case; volumes come from get_particle_volume as in
+    main.py:270.  The collider is the one main.py:276 always adds (plane z = 0.4, normal +z, friction 0)."""
+    c = CONFIG_SHAPES[name]
+    cloud = make_blob(c["n"], c["n_grid"], seed=seed)
+    args = sim_args(n_grid=c["n_grid"], grid_extent=2.0, material=c["material"], E=c["E"], nu=c["nu"], density=c["density"],
+                    gravity=c["gravity"], substep_dt=c["substep_dt"], frame_dt=c["frame_dt"])
+    args.boundary_conditions = c["bcs"]
+    ops = {"boundary_conditions": c["bcs"], "collider": {"point": (0.0, 0.0, 0.4), "normal": (0.0, 0.0, 1.0), "friction": 0.0}}
+    return cloud, args, ops

@@ -278,3 +278,32 @@ def test_full_size_properties(cuda_dev):
     assert torch.isfinite(x).all() and torch.isfinite(cov).all()
     RtR = torch.einsum("nji,njk->nik", R, R)
     assert (RtR - torch.eye(3, device=cuda_dev)).abs().max().item() < 1e-4     # R in O(3)
+
+
+@pytest.mark.gpu
+def test_lego_shaped_config_parity(cuda_dev):
+    """configs/lego.json by shape: 240,549 particles packed into a few thousand cells of a 50^3 grid
+    (hundreds per cell: the same-address contention regime of the named scenes), gravity -100, the config's
+    boundary conditions (one of them active on substep 0 only) and main.py's collider; volumes from
+    get_particle_volume as main.py:270 does.  20 substeps against the oracle."""
+    import torch
+    from internel_filling.filling import get_particle_volume
+    from oracle import mpm_oracle as O
+    cloud, args, ops = synthetic.config_workload("lego-like")
+    vol = get_particle_volume(torch.from_numpy(cloud["xyz"]).to(cuda_dev), args)
+    cloud["vol"] = vol.cpu().numpy()
+    assert np.allclose(cloud["vol"], O.particle_volume(cloud["xyz"], args.n_grid, args.grid_extent), rtol=1e-6)
+    g = make_gpu(cloud, args, cuda_dev, ops, strict_q1=False)
+    o = make_oracle(cloud, args, ops, strict_q1=False)
+    dt = args.substep_dt
+    S = 20
+    g.step(S, dt)
+    for _ in range(S):
+        o.p2g2p(dt)
+    g.postprocess(); o.postprocess()
+    st = g.mpm_state
+    x = st.particle_xyz.to_torch().cpu().numpy()
+    assert np.abs(x - o.in_original_order("particle_xyz")).max() < 1e-4 * float(o.dx)
+    assert rel_fro(st.particle_F_trial.to_torch().cpu().numpy(), o.in_original_order("particle_F_trial")) < 1e-4
+    assert rel_fro(st.particle_cov.to_torch().cpu().numpy(), o.in_original_order("particle_cov")) < 1e-4
+    assert abs(g.time - o.time) < 1e-12
