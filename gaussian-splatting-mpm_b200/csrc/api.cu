@@ -35,7 +35,11 @@ static int create_impl(mpmk_ctx* ctx, int device, int n_grid, double grid_extent
     ALLOC0(ctx, ctx->perm, cap * 4);
     ALLOC0(ctx, ctx->perm_alt, cap * 4);
     ctx->n_sort_ctas_cap = div_up((int64_t)cap, MPMK_SORT_CHUNK);
-    ALLOC0(ctx, ctx->sort_ctrl, ((size_t)8 + 4 * 512 + (size_t)4 * (1 << MPMK_MAX_RADIX_BITS) * ctx->n_sort_ctas_cap) * 4);
+    ALLOC0(ctx, ctx->sort_ctrl, ((size_t)8 + 4 * 512 + ((size_t)4 * (1 << MPMK_MAX_RADIX_BITS) + 2) * ctx->n_sort_ctas_cap) * 4);
+    for (int i = 0; i < 2; ++i) { ALLOC0(ctx, ctx->cs_mk[i], cap * 4); ALLOC0(ctx, ctx->cs_mv[i], cap * 4); }
+    ALLOC0(ctx, ctx->cs_mask, (cap / 32 + 2) * 4);
+    ALLOC0(ctx, ctx->cs_mprefix, (cap / 32 + 2) * 4);
+    ALLOC0(ctx, ctx->cs_cnt, (cap / 32 + 2) * 4);
     ALLOC0(ctx, ctx->hist_tot, 4 * 512 * 4);
     const size_t ntiles = (size_t)ctx->nt * ctx->nt * ctx->nt;
     ctx->items_cap = (int64_t)(cap / MPMK_ITEM_MIN + (cap < ntiles ? cap : ntiles) + 8);
@@ -70,6 +74,8 @@ extern "C" int mpmk_destroy(mpmk_ctx* ctx) {
     mpmk_mg_finalize(ctx);
     for (int i = 0; i < ctx->n_graphs; ++i) cudaGraphExecDestroy(ctx->graphs[i].exec);
     cudaFree(ctx->keys_alt); cudaFree(ctx->sorted_keys); cudaFree(ctx->perm); cudaFree(ctx->perm_alt);
+    for (int i = 0; i < 2; ++i) { cudaFree(ctx->cs_mk[i]); cudaFree(ctx->cs_mv[i]); }
+    cudaFree(ctx->cs_mask); cudaFree(ctx->cs_mprefix); cudaFree(ctx->cs_cnt);
     cudaFree(ctx->sort_ctrl); cudaFree(ctx->hist_tot); cudaFree(ctx->items); cudaFree(ctx->tile_list); cudaFree(ctx->tile_end); cudaFree(ctx->block_stamp);
     cudaFree(ctx->block_list[0]); cudaFree(ctx->block_list[1]); cudaFree(ctx->block_count[0]); cudaFree(ctx->block_count[1]);
     cudaFree(ctx->counters); cudaFree(ctx->dev_stamp);
@@ -93,6 +99,7 @@ extern "C" int mpmk_bind(mpmk_ctx* ctx, const mpmk_bindings* b) {
     if (!b->keys || !b->grid_in || !b->grid_out) MPMK_FAIL(ctx, MPMK_ERR_INVALID, "mpmk_bind: keys/grid_in/grid_out must be bound");
     ctx->b = *b;
     ctx->bound = true;
+    ctx->coherent = false;
     ctx->sorted_valid = false;
     ctx->prepared = false;
     ctx->ftrial_valid = false;
@@ -112,6 +119,7 @@ extern "C" int mpmk_set_count(mpmk_ctx* ctx, int64_t n, int current_set) {
         MPMK_FAIL(ctx, MPMK_ERR_INVALID, "mpmk_set_count: n=%lld capacity=%lld set=%d", (long long)n, (long long)ctx->capacity, current_set);
     ctx->n = n;
     ctx->cur = current_set;
+    ctx->coherent = false;
     ctx->sorted_valid = false;
     ctx->prepared = false;
     ctx->ftrial_valid = false;
@@ -200,9 +208,14 @@ extern "C" int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* op
     for (int i = 0; i < ctx->n_graphs; ++i) {
         mpmk_ctx::GraphEntry& g = ctx->graphs[i];
         if (g.n_steps == n_steps && g.dt == dt && g.cur == ctx->cur && g.cur_list == ctx->cur_list && g.flags == user_flags &&
-            g.n == ctx->n && memcmp(&g.ops, ops, sizeof(*ops)) == 0 && same_bindings(g.b, ctx->b)) {
+            g.n == ctx->n && g.coherent == ctx->coherent && g.sorted_keys == ctx->sorted_keys &&
+            memcmp(&g.ops, ops, sizeof(*ops)) == 0 && same_bindings(g.b, ctx->b)) {
             MPMK_CHECK(ctx, cudaGraphLaunch(g.exec, s));
             ctx->launches += 1;
+            ctx->coherent = g.end_coherent;
+            ctx->last_sort_coherent = g.end_last_sort_coherent;
+            ctx->sorted_keys = g.end_sorted_keys;
+            ctx->keys_alt = g.end_keys_alt;
             ctx->cur = (ctx->cur + n_steps) & 1;
             ctx->cur_list = (ctx->cur_list + n_steps) & 1;
             ctx->ftrial_valid = (user_flags & MPMK_WRITE_FTRIAL) != 0;
@@ -215,7 +228,7 @@ extern "C" int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* op
     mpmk_ctx::GraphEntry e;
     memset(&e, 0, sizeof(e));
     e.n_steps = n_steps; e.dt = dt; e.cur = ctx->cur; e.cur_list = ctx->cur_list; e.flags = user_flags; e.n = ctx->n;
-    e.ops = *ops; e.b = ctx->b;
+    e.ops = *ops; e.b = ctx->b; e.coherent = ctx->coherent; e.sorted_keys = ctx->sorted_keys;
     const int64_t launches_before = ctx->launches;
     cudaStream_t cs = ctx->cap_stream;
     MPMK_CHECK(ctx, cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
@@ -235,6 +248,7 @@ extern "C" int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* op
     cudaGraphDestroy(graph);
     MPMK_CHECK(ctx, ce);
     e.exec = exec;
+    e.end_coherent = ctx->coherent; e.end_last_sort_coherent = ctx->last_sort_coherent; e.end_sorted_keys = ctx->sorted_keys; e.end_keys_alt = ctx->keys_alt;
     if (ctx->n_graphs == 4) {  // evict the oldest
         cudaGraphExecDestroy(ctx->graphs[0].exec);
         for (int i = 1; i < 4; ++i) ctx->graphs[i - 1] = ctx->graphs[i];

@@ -65,6 +65,15 @@ struct mpmk_ctx {
     uint32_t* sorted_keys;   // result of last sort
     uint32_t* perm;          // result of last sort: physical slot of the r-th particle in sorted order
     uint32_t* perm_alt;
+    // coherent sort scratch (sort.cu): compacted movers (key, slot) ping-pong; per-32-slot-word mover mask, exclusive
+    // mover prefix and count of movers inserted in front of the word's stayers
+    uint32_t* cs_mk[2];
+    uint32_t* cs_mv[2];
+    uint32_t* cs_mask;
+    uint32_t* cs_mprefix;
+    uint32_t* cs_cnt;
+    bool last_sort_coherent; // which path the last mpmk_sort took
+    bool coherent;           // sorted_keys[r] is the OLD key of physical slot r of the current set (g2p wrote it in sorted order)
     uint32_t* sort_ctrl;     // one-sweep control block: tile counters, digit histograms, status words (sort.cu)
     uint32_t* hist_tot;      // [passes][512] exclusive digit bases
     int64_t n_sort_ctas_cap;
@@ -92,6 +101,12 @@ struct mpmk_ctx {
         uint32_t flags;
         int64_t n;
         mpmk_bindings b;
+        bool coherent;            // state the capture started from ...
+        uint32_t* sorted_keys;
+        bool end_coherent;        // ... and the state it leaves behind
+        bool end_last_sort_coherent;
+        uint32_t* end_sorted_keys;
+        uint32_t* end_keys_alt;
     } graphs[4];
     int n_graphs;
     cudaStream_t cap_stream;  // graphs are captured here (the legacy default stream cannot be captured)

@@ -342,6 +342,7 @@ int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s) {
     ctx->cur = dst;
     ctx->ftrial_valid = (ctx->prm.flags & MPMK_WRITE_FTRIAL) != 0;
     ctx->sorted_valid = false;  // the permutation referred to the old physical order
+    ctx->coherent = true;       // ... but sorted_keys[r] is now the old key of physical slot r (sort.cu, coherent sort)
     ctx->prepared = false;
     return 0;
 }

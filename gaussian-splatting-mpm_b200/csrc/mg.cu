@@ -124,6 +124,7 @@ extern "C" int mpmk_mg_set_count(mpmk_ctx* ctx, int64_t n) {
     if (!ctx) return MPMK_ERR_INVALID;
     if (n < 0 || n > ctx->capacity) MPMK_FAIL(ctx, MPMK_ERR_INVALID, "mpmk_mg_set_count: n=%lld capacity=%lld", (long long)n, (long long)ctx->capacity);
     ctx->n = n;
+    ctx->coherent = false;
     ctx->sorted_valid = false;
     ctx->prepared = false;
     return 0;

@@ -22,6 +22,7 @@ int mpmk_launch_keys(mpmk_ctx* ctx, cudaStream_t s) {
                                                ctx->inv_dx, ctx->n_grid, ctx->nt, ctx->counters);
     MPMK_LAUNCH_CHECK(ctx);
     ctx->sorted_valid = false;
+    ctx->coherent = false;   // the host rewrote positions: the old sorted keys say nothing about the new ones
     ctx->prepared = false;
     return 0;
 }
@@ -38,14 +39,17 @@ int mpmk_launch_keys(mpmk_ctx* ctx, cudaStream_t s) {
 #define OS_MASK 0x3fffffffu
 #define OS_MAX_PASSES 4
 // control block layout (uint32 words, zeroed once per sort): [0..3] tile counters per pass, [4] blocks done,
-// [8 ..] global digit histograms [OS_MAX_PASSES][512], then the status words [passes][ntiles][D]
+// [5],[6] chunk tickets of the two coherent-sort scans, [7] mover count, [8 ..] global digit histograms
+// [OS_MAX_PASSES][512], then the status words [passes][ntiles][D], then [2][ntiles] scan status words
 #define OS_CTRL_HIST 8
 #define OS_CTRL_STATUS (OS_CTRL_HIST + OS_MAX_PASSES * 512)
 
 template <int BITS>
-__global__ void __launch_bounds__(256) k_sort_digit_hist(const uint32_t* __restrict__ keys, int64_t n, int passes,
-                                                         uint32_t* __restrict__ ctrl, uint32_t* __restrict__ digit_base) {
+__global__ void __launch_bounds__(256) k_sort_digit_hist(const uint32_t* __restrict__ keys, int64_t n, const uint32_t* n_dev,
+                                                         int passes, uint32_t* __restrict__ ctrl,
+                                                         uint32_t* __restrict__ digit_base) {
     constexpr int D = 1 << BITS;
+    if (n_dev) n = (int64_t)*n_dev;   // coherent sort: the mover count is only known on the device
     __shared__ uint32_t h[OS_MAX_PASSES][D];
     __shared__ bool last;
     for (int i = threadIdx.x; i < OS_MAX_PASSES * D; i += 256) (&h[0][0])[i] = 0;
@@ -113,61 +117,68 @@ __global__ void __launch_bounds__(256) k_sort_digit_hist(const uint32_t* __restr
     }
 }
 
-template <int BITS>
-__global__ void __launch_bounds__(MPMK_SORT_CTA) k_sort_onesweep(const uint32_t* __restrict__ keys_in,
+// CTA threads rank ROUNDS keys each: 256 x 16 for the full sort; 1024 x 4 for the coherent sort's few movers, where
+// the latency of one tile, not throughput, is what a pass costs (same tile size, hence the same status layout)
+template <int BITS, int CTA, int ROUNDS>
+__global__ void __launch_bounds__(CTA) k_sort_onesweep(const uint32_t* __restrict__ keys_in,
                                                                  const uint32_t* __restrict__ vals_in,
                                                                  uint32_t* __restrict__ keys_out,
-                                                                 uint32_t* __restrict__ vals_out, int64_t n, int shift,
+                                                                 uint32_t* __restrict__ vals_out, int64_t n,
+                                                                 const uint32_t* n_dev, int shift,
                                                                  const uint32_t* __restrict__ digit_base,
                                                                  uint32_t* __restrict__ status, uint32_t* __restrict__ tile_counter) {
     constexpr int D = 1 << BITS;
-    constexpr int NW = MPMK_SORT_CTA / 32;
-    constexpr int DPT = (D + MPMK_SORT_CTA - 1) / MPMK_SORT_CTA;  // digits per thread (1 or 2)
-    __shared__ uint32_t wh[NW][D];
+    constexpr int CHUNK = CTA * ROUNDS;
+    static_assert(CHUNK == MPMK_SORT_CHUNK, "tile size is part of the control block layout");
+    constexpr int NW = CTA / 32;
+    constexpr int DPT = (D + CTA - 1) / CTA;  // digits per thread (1 or 2)
     __shared__ uint32_t lstart[D];   // tile-local first position of digit d
     __shared__ uint32_t gdelta[D];   // global position = local position + gdelta[d] (mod 2^32)
-    extern __shared__ uint32_t os_stage[];   // [2][MPMK_SORT_CHUNK]: the tile's keys and values in sorted order
+    extern __shared__ uint32_t os_stage[];   // [2][CHUNK]: the tile's keys and values in sorted order, then wh[NW][D]
     uint32_t* skey = os_stage;
-    uint32_t* sval = os_stage + MPMK_SORT_CHUNK;
-    __shared__ uint32_t part[MPMK_SORT_CTA];
+    uint32_t* sval = os_stage + CHUNK;
+    uint32_t (*wh)[D] = reinterpret_cast<uint32_t (*)[D]>(os_stage + 2 * CHUNK);   // per-warp digit counters
+    __shared__ uint32_t part[CTA];
     __shared__ uint32_t tile_s;
+    if (n_dev) n = (int64_t)*n_dev;   // the grid is sized for the worst case; surplus CTAs leave at once
     if (threadIdx.x == 0) tile_s = atomicAdd(tile_counter, 1u);
-    for (int i = threadIdx.x; i < NW * D; i += MPMK_SORT_CTA) (&wh[0][0])[i] = 0;
+    for (int i = threadIdx.x; i < NW * D; i += CTA) (&wh[0][0])[i] = 0;
     __syncthreads();
     const uint32_t tile = tile_s;
+    if ((int64_t)tile * CHUNK >= n) return;
     const int w = threadIdx.x >> 5;
     const unsigned lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
-    const int64_t tile_base = (int64_t)tile * MPMK_SORT_CHUNK;
-    const int tile_count = (int)min((int64_t)MPMK_SORT_CHUNK, n - tile_base);
-    uint32_t off[MPMK_SORT_ROUNDS];
+    const int64_t tile_base = (int64_t)tile * CHUNK;
+    const int tile_count = (int)min((int64_t)CHUNK, n - tile_base);
+    uint32_t off[ROUNDS];
     // the tile's keys and values arrive in the staging area by asynchronous 16-byte copies (no registers held
     // while they are in flight; the input tile is contiguous)
     {
-        const bool full = (tile_count == MPMK_SORT_CHUNK) && ((tile_base & 3) == 0);
+        const bool full = (tile_count == CHUNK) && ((tile_base & 3) == 0);
         if (full) {
 #pragma unroll
-            for (int q = 0; q < MPMK_SORT_CHUNK / (4 * MPMK_SORT_CTA); ++q) {
-                const int i4 = q * MPMK_SORT_CTA + threadIdx.x;  // index of a group of 4 words
+            for (int q = 0; q < CHUNK / (4 * CTA); ++q) {
+                const int i4 = q * CTA + threadIdx.x;  // index of a group of 4 words
                 cp_async16(skey + 4 * i4, keys_in + tile_base + 4 * i4);
                 if (vals_in) cp_async16(sval + 4 * i4, vals_in + tile_base + 4 * i4);
             }
             cp_async_commit();
         } else {
-            for (int i = threadIdx.x; i < MPMK_SORT_CHUNK; i += MPMK_SORT_CTA) {
+            for (int i = threadIdx.x; i < CHUNK; i += CTA) {
                 skey[i] = (i < tile_count) ? keys_in[tile_base + i] : 0xffffffffu;
                 if (vals_in) sval[i] = (i < tile_count) ? vals_in[tile_base + i] : 0u;
             }
         }
         if (!vals_in)
-            for (int i = threadIdx.x; i < MPMK_SORT_CHUNK; i += MPMK_SORT_CTA) sval[i] = (uint32_t)(tile_base + i);
+            for (int i = threadIdx.x; i < CHUNK; i += CTA) sval[i] = (uint32_t)(tile_base + i);
         cp_async_wait<0>();
         __syncthreads();
     }
-    const int seg = w * (32 * MPMK_SORT_ROUNDS);
+    const int seg = w * (32 * ROUNDS);
     // rank of every key among the same-digit keys of its warp's segment (segment order = key order)
 #pragma unroll
-    for (int r = 0; r < MPMK_SORT_ROUNDS; ++r) {
+    for (int r = 0; r < ROUNDS; ++r) {
         const int li = seg + r * 32 + (int)lane;
         const bool valid = li < tile_count;
         const uint32_t d = valid ? ((skey[li] >> shift) & (D - 1)) : (uint32_t)D;
@@ -184,7 +195,7 @@ __global__ void __launch_bounds__(MPMK_SORT_CTA) k_sort_onesweep(const uint32_t*
     uint32_t total[DPT];
 #pragma unroll
     for (int q = 0; q < DPT; ++q) {
-        const int d = threadIdx.x + q * MPMK_SORT_CTA;
+        const int d = threadIdx.x + q * CTA;
         total[q] = 0;
         if (d < D) {
             uint32_t run = 0;
@@ -202,25 +213,25 @@ __global__ void __launch_bounds__(MPMK_SORT_CTA) k_sort_onesweep(const uint32_t*
         // thread t holds digits t and t+CTA: scan in digit order needs two sweeps when DPT == 2
         part[threadIdx.x] = total[0];
         __syncthreads();
-        for (int o = 1; o < MPMK_SORT_CTA; o <<= 1) {
+        for (int o = 1; o < CTA; o <<= 1) {
             const uint32_t v = (threadIdx.x >= o) ? part[threadIdx.x - o] : 0u;
             __syncthreads();
             part[threadIdx.x] += v;
             __syncthreads();
         }
-        const uint32_t lo_total = part[MPMK_SORT_CTA - 1];  // count of digits [0, CTA)
+        const uint32_t lo_total = part[CTA - 1];  // count of digits [0, CTA)
         if (threadIdx.x < D) lstart[threadIdx.x] = part[threadIdx.x] - total[0];
         __syncthreads();
         if (DPT == 2) {
             part[threadIdx.x] = total[DPT - 1];
             __syncthreads();
-            for (int o = 1; o < MPMK_SORT_CTA; o <<= 1) {
+            for (int o = 1; o < CTA; o <<= 1) {
                 const uint32_t v = (threadIdx.x >= o) ? part[threadIdx.x - o] : 0u;
                 __syncthreads();
                 part[threadIdx.x] += v;
                 __syncthreads();
             }
-            if (threadIdx.x + MPMK_SORT_CTA < D) lstart[threadIdx.x + MPMK_SORT_CTA] = lo_total + part[threadIdx.x] - total[DPT - 1];
+            if (threadIdx.x + CTA < D) lstart[threadIdx.x + CTA] = lo_total + part[threadIdx.x] - total[DPT - 1];
             __syncthreads();
         }
         (void)s;
@@ -228,7 +239,7 @@ __global__ void __launch_bounds__(MPMK_SORT_CTA) k_sort_onesweep(const uint32_t*
     // decoupled look-back: count of digit d in all earlier tiles
 #pragma unroll
     for (int q = 0; q < DPT; ++q) {
-        const int d = threadIdx.x + q * MPMK_SORT_CTA;
+        const int d = threadIdx.x + q * CTA;
         if (d < D) {
             uint32_t excl = 0;
             if (tile > 0) {
@@ -248,16 +259,16 @@ __global__ void __launch_bounds__(MPMK_SORT_CTA) k_sort_onesweep(const uint32_t*
     __syncthreads();
     // re-stage the tile in sorted order (through registers: the staging area is rewritten in place)
     {
-        uint32_t key[MPMK_SORT_ROUNDS], val[MPMK_SORT_ROUNDS];
+        uint32_t key[ROUNDS], val[ROUNDS];
 #pragma unroll
-        for (int r = 0; r < MPMK_SORT_ROUNDS; ++r) {
+        for (int r = 0; r < ROUNDS; ++r) {
             const int li = seg + r * 32 + (int)lane;
             key[r] = skey[li];
             val[r] = sval[li];
         }
         __syncthreads();
 #pragma unroll
-        for (int r = 0; r < MPMK_SORT_ROUNDS; ++r) {
+        for (int r = 0; r < ROUNDS; ++r) {
             if (seg + r * 32 + (int)lane < tile_count) {
                 const uint32_t d = (key[r] >> shift) & (D - 1);
                 const uint32_t lp = lstart[d] + wh[w][d] + off[r];
@@ -269,8 +280,8 @@ __global__ void __launch_bounds__(MPMK_SORT_CTA) k_sort_onesweep(const uint32_t*
     __syncthreads();
     // write out: consecutive threads hold consecutive positions of the same digit run
 #pragma unroll
-    for (int r = 0; r < MPMK_SORT_ROUNDS; ++r) {
-        const int i = r * MPMK_SORT_CTA + threadIdx.x;
+    for (int r = 0; r < ROUNDS; ++r) {
+        const int i = r * CTA + threadIdx.x;
         if (i < tile_count) {
             const uint32_t k = skey[i];
             const uint32_t pos = (uint32_t)i + gdelta[(k >> shift) & (D - 1)];
@@ -280,28 +291,321 @@ __global__ void __launch_bounds__(MPMK_SORT_CTA) k_sort_onesweep(const uint32_t*
     }
 }
 
+
+// ---- coherent sort ----------------------------------------------------------------------
+// g2p writes the particles in sorted order, so in the next substep the OLD key of physical slot r is still
+// sitting in sorted_keys[r], and all but the few particles that changed cell ("movers", keys[r] != okeys[r]) are
+// already in order among themselves.  The stable sort by (key, slot) is then the merge of
+//     stayers -- sorted as they lie -- and movers -- compacted in slot order, then radix-sorted by key (stable),
+// and the merge needs no comparisons between the two lists beyond searches in the old sorted keys:
+//   mover (k, j): every stayer in a slot < x sorts before it, x = min(max(j, lower_bound(okeys, k)), upper_bound(okeys, k))
+//                 (stayers keep their old key, and okeys is non-decreasing), so with t = its rank among the sorted
+//                 movers and S(x) = stayers in slots [0, x):      position = t + S(x);
+//   stayer i:     the movers in front of it are those with x <= i (x is non-decreasing in t):
+//                                                                 position = S(i) + #{t : x_t <= i}.
+// S comes from a chained scan of the mover flags (k_cs_flag_scan), #{t : x_t <= i} from a second chained scan over
+// per-word insert counts (k_cs_place_stayers).  The result is the permutation a CPU stable sort produces, for ANY
+// non-decreasing okeys; nearly-unchanged keys only make it cheap (every pass touches N keys once instead of
+// three scatter passes).  Correctness does not depend on the mover fraction, only the speed does.
+#define CS_CHUNK 4096   // slots per CTA of the scans = 128 mask words, 16 per warp
+#define CS_THREADS 256
+#define CS_CTRL_TICKET_A 5
+#define CS_CTRL_TICKET_B 6
+#define CS_CTRL_MOVERS 7
+
+// Warp-parallel decoupled look-back: sum of the aggregates of chunks [0, chunk).  Chunks are handed out by ticket,
+// so every predecessor has at least started.
+__device__ __forceinline__ uint32_t cs_lookback(const uint32_t* status, uint32_t chunk, unsigned lane) {
+    uint32_t excl = 0;
+    int64_t t = (int64_t)chunk - 1;
+    while (t >= 0) {
+        const int64_t mine = t - (int64_t)lane;
+        uint32_t v;
+        bool ready;
+        do {
+            v = (mine >= 0) ? *((volatile const uint32_t*)&status[mine]) : OS_FLAG_INC;   // before chunk 0: prefix 0
+            ready = (v & (OS_FLAG_AGG | OS_FLAG_INC)) != 0u;
+        } while (!__all_sync(0xffffffffu, ready));
+        const unsigned inc = __ballot_sync(0xffffffffu, (v & OS_FLAG_INC) != 0u);
+        const int first = __ffs(inc) - 1;   // nearest predecessor holding an inclusive prefix (-1: none in this window)
+        const uint32_t c = (inc == 0u || (int)lane <= first) ? (v & OS_MASK) : 0u;
+        excl += __reduce_add_sync(0xffffffffu, c);
+        if (inc) break;
+        t -= 32;
+    }
+    return excl;
+}
+
+// CTA-wide exclusive offsets of the per-word counts `pc` (held by lanes 0..15 of each warp), chained across chunks.
+// Returns, for lanes 0..15, the global exclusive prefix of that lane's word; *total_out = inclusive prefix of the chunk.
+__device__ __forceinline__ uint32_t cs_chunk_scan(uint32_t pc, uint32_t chunk, uint32_t* status, uint32_t* wsum, uint32_t* excl_s,
+                                                  uint32_t* total_out) {
+    const int w = threadIdx.x >> 5;
+    const unsigned lane = threadIdx.x & 31;
+    uint32_t inc = pc;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+        if ((int)lane >= o) inc += v;
+    }
+    if (lane == 31) wsum[w] = inc;
+    __syncthreads();
+    uint32_t wex = 0, total = 0;
+#pragma unroll
+    for (int ww = 0; ww < CS_THREADS / 32; ++ww) { const uint32_t t = wsum[ww]; if (ww < w) wex += t; total += t; }
+    if (w == 0) {
+        if (lane == 0) atomicExch(&status[chunk], total | (chunk == 0 ? OS_FLAG_INC : OS_FLAG_AGG));
+        const uint32_t ex = chunk ? cs_lookback(status, chunk, lane) : 0u;
+        if (lane == 0) {
+            if (chunk) atomicExch(&status[chunk], (ex + total) | OS_FLAG_INC);
+            *excl_s = ex;
+        }
+    }
+    __syncthreads();
+    *total_out = *excl_s + total;
+    return *excl_s + wex + inc - pc;
+}
+
+__global__ void __launch_bounds__(CS_THREADS) k_cs_flag_scan(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ okeys,
+                                                             int64_t n, uint32_t* __restrict__ ctrl, uint32_t* __restrict__ status,
+                                                             uint32_t* __restrict__ mask, uint32_t* __restrict__ mprefix,
+                                                             uint32_t* __restrict__ cnt, uint32_t* __restrict__ mk,
+                                                             uint32_t* __restrict__ mv, int bits, int passes,
+                                                             uint32_t* __restrict__ digit_base) {
+    __shared__ uint32_t chunk_s, excl_s;
+    __shared__ uint32_t wsum[CS_THREADS / 32];
+    if (threadIdx.x == 0) chunk_s = atomicAdd(&ctrl[CS_CTRL_TICKET_A], 1u);
+    __syncthreads();
+    const uint32_t chunk = chunk_s;
+    const int w = threadIdx.x >> 5;
+    const unsigned lane = threadIdx.x & 31;
+    const unsigned lt = (1u << lane) - 1u;
+    const int64_t wbase = (int64_t)chunk * CS_CHUNK + (int64_t)w * 512;
+    uint32_t k[16];
+    uint32_t myword = 0;   // lane r < 16 keeps the mover mask of the warp's r-th word
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+        const int64_t slot = wbase + r * 32 + lane;
+        bool moved = false;
+        k[r] = 0;
+        if (slot < n) { k[r] = keys[slot]; moved = (k[r] != okeys[slot]); }
+        const unsigned m = __ballot_sync(0xffffffffu, moved);
+        if ((int)lane == r) myword = m;
+    }
+    const uint32_t pc = __popc(myword);
+    uint32_t total;
+    const uint32_t wordex = cs_chunk_scan(pc, chunk, status, wsum, &excl_s, &total);
+    if (threadIdx.x == 0 && (int64_t)(chunk + 1) * CS_CHUNK >= n) ctrl[CS_CTRL_MOVERS] = total;
+    const int64_t word0 = wbase >> 5;
+    if (lane < 16 && (word0 + lane) * 32 < n) {
+        mask[word0 + lane] = myword;
+        mprefix[word0 + lane] = wordex;
+        cnt[word0 + lane] = 0u;
+    }
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+        const unsigned m = __shfl_sync(0xffffffffu, myword, r);
+        const uint32_t ex = __shfl_sync(0xffffffffu, wordex, r);
+        if ((m >> lane) & 1u) {
+            const uint32_t c = ex + __popc(m & lt);
+            mk[c] = k[r];
+            mv[c] = (uint32_t)(wbase + r * 32 + lane);
+            // digit histograms of the movers for every radix pass (few movers: straight to the global table)
+            for (int p = 0; p < passes; ++p) atomicAdd(&ctrl[OS_CTRL_HIST + p * 512 + ((k[r] >> (p * bits)) & ((1u << bits) - 1u))], 1u);
+        }
+    }
+    // the last CTA to finish turns the histograms into exclusive digit bases (as k_sort_digit_hist does)
+    __shared__ bool last;
+    __shared__ uint32_t part[CS_THREADS];
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) last = (atomicAdd(&ctrl[4], 1u) == gridDim.x - 1);
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    const int D = 1 << bits;
+    for (int p = 0; p < passes; ++p) {
+        const volatile uint32_t* g = ctrl + OS_CTRL_HIST + p * 512;
+        const uint32_t a = (2 * (int)threadIdx.x < D) ? g[2 * threadIdx.x] : 0u;
+        const uint32_t b = (2 * (int)threadIdx.x + 1 < D) ? g[2 * threadIdx.x + 1] : 0u;
+        part[threadIdx.x] = a + b;
+        __syncthreads();
+        for (int o = 1; o < CS_THREADS; o <<= 1) {
+            const uint32_t v = ((int)threadIdx.x >= o) ? part[threadIdx.x - o] : 0u;
+            __syncthreads();
+            part[threadIdx.x] += v;
+            __syncthreads();
+        }
+        const uint32_t ex = part[threadIdx.x] - (a + b);
+        if (2 * (int)threadIdx.x < D) digit_base[p * 512 + 2 * threadIdx.x] = ex;
+        if (2 * (int)threadIdx.x + 1 < D) digit_base[p * 512 + 2 * threadIdx.x + 1] = ex + a;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) k_cs_place_movers(const uint32_t* __restrict__ mk, const uint32_t* __restrict__ mv,
+                                                         const uint32_t* __restrict__ ctrl, const uint32_t* __restrict__ okeys,
+                                                         int64_t n, const uint32_t* __restrict__ mask,
+                                                         const uint32_t* __restrict__ mprefix, uint32_t* __restrict__ cnt,
+                                                         uint32_t* __restrict__ mx, uint32_t* __restrict__ out_keys,
+                                                         uint32_t* __restrict__ out_perm) {
+    const uint32_t M = ctrl[CS_CTRL_MOVERS];
+    const uint32_t N = (uint32_t)n;
+    // first level of the searches: 1024 evenly spaced old keys in shared memory
+    __shared__ uint32_t samp[1024];
+    const uint32_t stride = (N + 1023u) / 1024u;
+    for (uint32_t i = threadIdx.x; i < 1024u; i += blockDim.x) {
+        const uint64_t idx = (uint64_t)i * stride;
+        samp[i] = idx < N ? okeys[idx] : 0xffffffffu;
+    }
+    __syncthreads();
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < M; t += gridDim.x * blockDim.x) {
+        const uint32_t kj = mk[t], j = mv[t];
+        // A mover's new key differs from its old one.  Moved up (old < new): every slot up to j holds a smaller old
+        // key, so x = lower_bound(okeys, kj) > j.  Moved down: x = upper_bound(okeys, kj) <= j.  One search either way.
+        const bool up = okeys[j] < kj;
+        uint32_t lo = 0, hi = 1024;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            const uint32_t v = samp[mid];
+            if (up ? (v < kj) : (v <= kj)) lo = mid + 1; else hi = mid;
+        }
+        // the answer lies in ((lo-1)*stride, lo*stride]
+        const uint64_t whi = (uint64_t)lo * stride;
+        hi = whi < N ? (uint32_t)whi : N;
+        lo = lo ? (lo - 1u) * stride + 1u : 0u;
+        if (up) lo = max(lo, j + 1u); else hi = min(hi, j);
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            const uint32_t v = okeys[mid];
+            if (up ? (v < kj) : (v <= kj)) lo = mid + 1; else hi = mid;
+        }
+        const uint32_t x = lo;
+        const uint32_t movers_before = (x >= N) ? M : mprefix[x >> 5] + __popc(mask[x >> 5] & ((1u << (x & 31u)) - 1u));
+        const uint32_t pos = t + (x - movers_before);
+        out_keys[pos] = kj;
+        out_perm[pos] = j;
+        mx[t] = x;
+        if (x < N) atomicAdd(&cnt[x >> 5], 1u);
+    }
+}
+
+__global__ void __launch_bounds__(CS_THREADS) k_cs_place_stayers(const uint32_t* __restrict__ keys, int64_t n,
+                                                                 uint32_t* __restrict__ ctrl, uint32_t* __restrict__ status,
+                                                                 const uint32_t* __restrict__ mask,
+                                                                 const uint32_t* __restrict__ mprefix,
+                                                                 const uint32_t* __restrict__ cnt, const uint32_t* __restrict__ mx,
+                                                                 uint32_t* __restrict__ out_keys, uint32_t* __restrict__ out_perm) {
+    __shared__ uint32_t chunk_s, excl_s;
+    __shared__ uint32_t wsum[CS_THREADS / 32];
+    if (threadIdx.x == 0) chunk_s = atomicAdd(&ctrl[CS_CTRL_TICKET_B], 1u);
+    __syncthreads();
+    const uint32_t chunk = chunk_s;
+    const int w = threadIdx.x >> 5;
+    const unsigned lane = threadIdx.x & 31;
+    const unsigned lt = (1u << lane) - 1u;
+    const int64_t wbase = (int64_t)chunk * CS_CHUNK + (int64_t)w * 512;
+    const int64_t word0 = wbase >> 5;
+    // issue the key loads before the chained scan so that they overlap the look-back
+    uint32_t k[16];
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+        const int64_t slot = wbase + r * 32 + lane;
+        k[r] = (slot < n) ? keys[slot] : 0u;
+    }
+    uint32_t pc = 0, myword = 0, mypre = 0;
+    if (lane < 16 && (word0 + lane) * 32 < n) { pc = cnt[word0 + lane]; myword = mask[word0 + lane]; mypre = mprefix[word0 + lane]; }
+    uint32_t total;
+    const uint32_t cw = cs_chunk_scan(pc, chunk, status, wsum, &excl_s, &total);   // movers in front of the word's first slot
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+        const int64_t slot = wbase + r * 32 + lane;
+        const unsigned m = __shfl_sync(0xffffffffu, myword, r);
+        const uint32_t c0 = __shfl_sync(0xffffffffu, cw, r);
+        const uint32_t nc = __shfl_sync(0xffffffffu, pc, r);
+        const uint32_t mp = __shfl_sync(0xffffffffu, mypre, r);
+        if (slot < n && !((m >> lane) & 1u)) {
+            uint32_t c = c0;
+            for (uint32_t e = 0; e < nc; ++e) {   // the movers inserted inside this word (x sorted: stop at the first one beyond)
+                if (mx[c0 + e] <= (uint32_t)slot) ++c; else break;
+            }
+            const uint32_t pos = ((uint32_t)slot - (mp + __popc(m & lt))) + c;
+            out_keys[pos] = k[r];
+            out_perm[pos] = (uint32_t)slot;
+        }
+    }
+}
+
+template <int BITS>
+static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s) {
+    constexpr int D = 1 << BITS;
+    const int ntiles = div_up(ctx->n, MPMK_SORT_CHUNK);   // == chunks of the scans (CS_CHUNK == MPMK_SORT_CHUNK)
+    static_assert(CS_CHUNK == MPMK_SORT_CHUNK, "the scans and the radix tiles share the control block sizing");
+    const size_t radix_status = (size_t)passes * ntiles * D;
+    const size_t ctrl_words = OS_CTRL_STATUS + radix_status + 2 * (size_t)ntiles;
+    MPMK_CHECK(ctx, cudaMemsetAsync(ctx->sort_ctrl, 0, ctrl_words * 4, s));
+    uint32_t* ctrl = ctx->sort_ctrl;
+    uint32_t* status_a = ctrl + OS_CTRL_STATUS + radix_status;
+    uint32_t* status_b = status_a + ntiles;
+    const uint32_t* okeys = ctx->sorted_keys;
+    const uint32_t* keys = (const uint32_t*)ctx->b.keys;
+    const int first = passes & 1;   // the compacted movers start in this buffer so that the last radix pass lands in buffer 0
+    k_cs_flag_scan<<<ntiles, CS_THREADS, 0, s>>>(keys, okeys, ctx->n, ctrl, status_a, ctx->cs_mask, ctx->cs_mprefix, ctx->cs_cnt,
+                                                 ctx->cs_mk[first], ctx->cs_mv[first], BITS, passes, ctx->hist_tot);
+    MPMK_LAUNCH_CHECK(ctx);
+    const uint32_t* m_dev = ctrl + CS_CTRL_MOVERS;
+    constexpr int stage_bytes = 2 * MPMK_SORT_CHUNK * 4 + (1024 / 32) * D * 4;   // staging + per-warp digit counters
+    static bool attr_set = false;
+    if (!attr_set) {
+        MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 1024, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, stage_bytes));
+        attr_set = true;
+    }
+    int in = first;
+    for (int p = 0; p < passes; ++p) {
+        const int o = 1 - in;
+        k_sort_onesweep<BITS, 1024, 4><<<ntiles, 1024, stage_bytes, s>>>(ctx->cs_mk[in], ctx->cs_mv[in], ctx->cs_mk[o], ctx->cs_mv[o], 0, m_dev,
+                                                               p * BITS, ctx->hist_tot + p * 512,
+                                                               ctrl + OS_CTRL_STATUS + (size_t)p * ntiles * D, ctrl + p);
+        MPMK_LAUNCH_CHECK(ctx);
+        in = o;
+    }
+    // sorted movers are in buffer `in` (== 0); the other key buffer is free and receives x_t
+    uint32_t* mx = ctx->cs_mk[1 - in];
+    k_cs_place_movers<<<ctx->sm_count * 4, 256, 0, s>>>(ctx->cs_mk[in], ctx->cs_mv[in], ctrl, okeys, ctx->n, ctx->cs_mask, ctx->cs_mprefix,
+                                                        ctx->cs_cnt, mx, ctx->keys_alt, ctx->perm);
+    MPMK_LAUNCH_CHECK(ctx);
+    k_cs_place_stayers<<<ntiles, CS_THREADS, 0, s>>>(keys, ctx->n, ctrl, status_b, ctx->cs_mask, ctx->cs_mprefix, ctx->cs_cnt, mx,
+                                                     ctx->keys_alt, ctx->perm);
+    MPMK_LAUNCH_CHECK(ctx);
+    uint32_t* t = ctx->sorted_keys; ctx->sorted_keys = ctx->keys_alt; ctx->keys_alt = t;
+    ctx->last_sort_coherent = true;
+    return 0;
+}
+
 template <int BITS>
 static int sort_all(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     constexpr int D = 1 << BITS;
     const int ntiles = div_up(ctx->n, MPMK_SORT_CHUNK);
+    if (ctx->coherent && !(ctx->prm.flags & MPMK_SORT_FULL)) return sort_coherent<BITS>(ctx, passes, s);
+    ctx->last_sort_coherent = false;
     const size_t ctrl_words = OS_CTRL_STATUS + (size_t)passes * ntiles * D;
     MPMK_CHECK(ctx, cudaMemsetAsync(ctx->sort_ctrl, 0, ctrl_words * 4, s));
     int hgrid = ntiles < ctx->sm_count * 4 ? ntiles : ctx->sm_count * 4;
-    k_sort_digit_hist<BITS><<<hgrid, 256, 0, s>>>((const uint32_t*)ctx->b.keys, ctx->n, passes, ctx->sort_ctrl, ctx->hist_tot);
+    k_sort_digit_hist<BITS><<<hgrid, 256, 0, s>>>((const uint32_t*)ctx->b.keys, ctx->n, nullptr, passes, ctx->sort_ctrl, ctx->hist_tot);
     MPMK_LAUNCH_CHECK(ctx);
     uint32_t* kb[2] = {ctx->sorted_keys, ctx->keys_alt};
     uint32_t* vb[2] = {ctx->perm, ctx->perm_alt};
     const uint32_t* kin = (const uint32_t*)ctx->b.keys;
     const uint32_t* vin = nullptr;
-    constexpr int stage_bytes = 2 * MPMK_SORT_CHUNK * 4;
-    static bool attr_set = false;  // static + dynamic shared memory exceeds 48 KB for 9-bit digits: opt in once
+    constexpr int stage_bytes = 2 * MPMK_SORT_CHUNK * 4 + (256 / 32) * D * 4;
+    static bool attr_set = false;  // more than 48 KB of shared memory: opt in once
     if (!attr_set) {
-        MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, stage_bytes));
+        MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 256, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, stage_bytes));
         attr_set = true;
     }
     for (int p = 0; p < passes; ++p) {
         const int o = (passes - 1 - p) & 1;
-        k_sort_onesweep<BITS><<<ntiles, MPMK_SORT_CTA, stage_bytes, s>>>(kin, vin, kb[o], vb[o], ctx->n, p * BITS, ctx->hist_tot + p * 512,
+        k_sort_onesweep<BITS, 256, 16><<<ntiles, 256, stage_bytes, s>>>(kin, vin, kb[o], vb[o], ctx->n, nullptr, p * BITS, ctx->hist_tot + p * 512,
                                                                ctx->sort_ctrl + OS_CTRL_STATUS + (size_t)p * ntiles * D,
                                                                ctx->sort_ctrl + p);
         MPMK_LAUNCH_CHECK(ctx);
@@ -326,6 +630,19 @@ int mpmk_launch_sort(mpmk_ctx* ctx, cudaStream_t s) {
     }
     if (rc) return rc;
     ctx->sorted_valid = true;
+    ctx->coherent = false;   // sorted_keys now holds the NEW keys; the next g2p re-establishes the relation
     ctx->prepared = false;
+    return 0;
+}
+
+extern "C" int mpmk_sort_info(mpmk_ctx* ctx, int* coherent_out, int64_t* movers_out, void* stream) {
+    if (!ctx || !ctx->bound) return MPMK_ERR_STATE;
+    uint32_t m = 0;
+    if (ctx->last_sort_coherent) {
+        MPMK_CHECK(ctx, cudaMemcpyAsync(&m, ctx->sort_ctrl + CS_CTRL_MOVERS, 4, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+        MPMK_CHECK(ctx, cudaStreamSynchronize((cudaStream_t)stream));
+    }
+    if (coherent_out) *coherent_out = ctx->last_sort_coherent ? 1 : 0;
+    if (movers_out) *movers_out = ctx->last_sort_coherent ? (int64_t)m : ctx->n;
     return 0;
 }

@@ -13,7 +13,7 @@ _ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB_PATH = os.environ.get("MPMK_LIB") or os.path.join(_ROOT, "lib", "libmpmk.so")
 
 MAT_JELLY, MAT_METAL, MAT_SAND, MAT_FOAM, MAT_FLUID, MAT_PLASTICINE = range(6)
-STRICT_Q1, STRICT_Q3, WRITE_FTRIAL, TRACK_COV = 1, 2, 4, 8
+STRICT_Q1, STRICT_Q3, WRITE_FTRIAL, TRACK_COV, SORT_FULL = 1, 2, 4, 8, 16
 OP_FIXED_CUBE, OP_COLLIDER = 0, 1
 MAX_GRID_OPS, MAX_IMPULSES = 16, 8
 
@@ -104,6 +104,7 @@ def lib():
         "mpmk_constitutive": (i, [vp, f, vp]),
         "mpmk_sort": (i, [vp, vp]),
         "mpmk_get_sort_result": (i, [vp, vp, vp, vp]),
+        "mpmk_sort_info": (i, [vp, C.POINTER(i), C.POINTER(i64), vp]),
         "mpmk_prepare_grid": (i, [vp, vp]),
         "mpmk_p2g": (i, [vp, f, C.POINTER(SubstepOps), vp]),
         "mpmk_grid_update": (i, [vp, f, C.POINTER(SubstepOps), vp]),

@@ -52,6 +52,7 @@ extern "C" {
 #define MPMK_STRICT_Q3 2u  /* constitutive_models.py:256: foam F through Hadamard     */
 #define MPMK_WRITE_FTRIAL 4u /* g2p also stores F_trial (needed by export for plastic)  */
 #define MPMK_TRACK_COV 8u  /* g2p applies update_cov every substep (utils.py:187-215) */
+#define MPMK_SORT_FULL 16u /* always run the full radix sort (no merge of the few particles that changed cell) */
 
 typedef struct mpmk_ctx mpmk_ctx;
 
@@ -159,10 +160,15 @@ MPMK_API int mpmk_compute_keys(mpmk_ctx* ctx, void* stream);
 MPMK_API int mpmk_constitutive(mpmk_ctx* ctx, float dt, void* stream);
 
 /* ---- the substep, stage by stage (solver.py:27-52) ------------------------ */
-/* stable LSD radix sort of (key, slot) by key; results stay in library scratch */
+/* stable sort of (key, slot) by key; results stay in library scratch.  Full LSD radix sort, or -- when the
+ * previous g2p left the particles in sorted order -- a radix sort of only the particles whose cell changed,
+ * merged with the rest; both produce the permutation of a CPU stable sort, bit for bit                   */
 MPMK_API int mpmk_sort(mpmk_ctx* ctx, void* stream);
 /* copy the last sort's sorted keys / permutation (uint32[n]) to caller buffers */
 MPMK_API int mpmk_get_sort_result(mpmk_ctx* ctx, void* sorted_keys_dev, void* perm_dev, void* stream);
+/* which path the last mpmk_sort took (1 = merge of the particles that changed cell, 0 = full radix sort) and how
+ * many (key, slot) pairs went through the radix passes; synchronises `stream`                              */
+MPMK_API int mpmk_sort_info(mpmk_ctx* ctx, int* coherent_out, int64_t* movers_out, void* stream);
 /* model.py:124-127 reset_grid_state, restricted to the blocks the previous
  * substep touched; then tile work list + active-block list of this substep   */
 MPMK_API int mpmk_prepare_grid(mpmk_ctx* ctx, void* stream);

@@ -214,6 +214,61 @@ def test_trajectory_parity(cuda_dev, material, strict, S):
     assert np.array_equal(ids[_sorted_state(g)[1]], o.order)
 
 
+def _sort_info(sim):
+    coh, mov = C.c_int(0), C.c_int64(0)
+    sim._backend.ctx.call("mpmk_sort_info", C.byref(coh), C.byref(mov), _stream())
+    return coh.value, mov.value
+
+
+@pytest.mark.parametrize("n_grid,lo,cn,ppc,omega,dt,material", [
+    (64, (22, 22, 22), (20, 20, 20), 8, (0.0, 0.0, 2.0), 4e-4, "jelly"),     # slow spin: ~1 % of the keys change per substep
+    (64, (22, 22, 22), (20, 20, 20), 8, (3.0, -4.0, 40.0), 4e-4, "sand"),    # fast: a large fraction moves, tiles are crossed
+    (50, (13, 13, 13), (12, 12, 12), 40, (0.0, 9.0, 25.0), 2e-4, "jelly"),   # 40 per cell: long equal-key runs, n_grid % 4 != 0
+    (16, (5, 5, 5), (3, 3, 3), 13, (0.0, 0.0, 30.0), 1e-3, "jelly"),         # ragged, less than one chunk
+    (128, (44, 44, 44), (40, 40, 40), 8, (1.0, 2.0, 12.0), 2e-4, "jelly"),   # 512 k particles: 125 chained chunks
+])
+def test_coherent_sort_bit_exact(cuda_dev, n_grid, lo, cn, ppc, omega, dt, material):
+    """After a g2p the library merges the few particles whose cell changed into the order the rest already has
+    (csrc/sort.cu, coherent sort).  The permutation and the sorted keys must be those of a CPU stable sort of the
+    same keys, bit for bit, substep after substep."""
+    import torch
+    cloud = synthetic.make_cloud(n_grid, 2.0, lo, cn, ppc=ppc, seed=21, omega=omega)
+    args = synthetic.sim_args(n_grid=n_grid, material=material, substep_dt=dt)
+    g = make_gpu(cloud, args, cuda_dev)
+    n = g.n_particles
+    b = g._backend
+    seen_coherent, movers = 0, []
+    for s in range(12):
+        g.p2g2p(dt) if s % 3 else g.step(2, dt)     # eager substeps and graph batches both end in a g2p
+        torch.cuda.synchronize()
+        keys = b.keys[:n].cpu().numpy().view(np.uint32).copy()
+        sk, pm = _sorted_state(g)
+        coh, mov = _sort_info(g)
+        seen_coherent += coh
+        movers.append(mov)
+        ref = np.argsort(keys, kind="stable").astype(np.uint32)
+        assert np.array_equal(pm, ref), f"substep {s}: permutation differs (coherent={coh}, movers={mov})"
+        assert np.array_equal(sk, keys[ref])
+    assert seen_coherent == 12, "the merge path did not run"
+    assert max(movers) > 0 and max(movers) < n
+
+
+def test_coherent_sort_equals_full_sort_trajectory(cuda_dev):
+    """same particle order => same trajectories: MPMK_SORT_FULL against the default (only the order of the float
+    atomics between warps may differ)"""
+    cloud, args = small_cloud(n_grid=40, cells_lo=(12, 12, 12), cells_n=(8, 8, 8), material="metal")
+    ops = synthetic.block_ops(40, 2.0, (12, 12, 12), (8, 8, 8))
+    a = make_gpu(cloud, args, cuda_dev, ops)
+    b = make_gpu(cloud, args, cuda_dev, ops)
+    b.set_parameters(sort_full=True)
+    a.step(30, 1e-4); b.step(30, 1e-4)
+    assert _sort_info(a)[0] == 1 and _sort_info(b)[0] == 0
+    assert np.array_equal(a._backend.ids().cpu().numpy(), b._backend.ids().cpu().numpy())   # same particle in every slot
+    xa, ca, _ = a.export(); xb, cb, _ = b.export()
+    assert (xa - xb).abs().max().item() <= 2.4e-7
+    assert rel_fro(ca.cpu().numpy(), cb.cpu().numpy()) < 1e-5
+
+
 def test_substeps_graph_equals_loop(cuda_dev):
     cloud, args = small_cloud(n_grid=40, cells_lo=(12, 12, 12), cells_n=(8, 8, 8), material="metal")
     ops = synthetic.block_ops(40, 2.0, (12, 12, 12), (8, 8, 8))
