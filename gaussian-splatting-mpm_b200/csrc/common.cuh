@@ -75,7 +75,7 @@ struct mpmk_ctx {
     bool last_sort_coherent; // which path the last mpmk_sort took
     bool coherent;           // sorted_keys[r] is the OLD key of physical slot r of the current set (g2p wrote it in sorted order)
     uint32_t* sort_ctrl;     // one-sweep control block: tile counters, digit histograms, status words (sort.cu)
-    uint32_t* hist_tot;      // [passes][512] exclusive digit bases
+    uint32_t* hist_tot;      // 2048 words: the 1024 evenly spaced old keys the coherent sort searches first
     int64_t n_sort_ctas_cap;
     uint4* items;            // {begin, count, tile, 0}
     uint2* tile_list;        // non-empty tiles of the current sort: {tile, first sorted index}

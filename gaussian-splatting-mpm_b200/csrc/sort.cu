@@ -46,12 +46,10 @@ int mpmk_launch_keys(mpmk_ctx* ctx, cudaStream_t s) {
 
 template <int BITS>
 __global__ void __launch_bounds__(256) k_sort_digit_hist(const uint32_t* __restrict__ keys, int64_t n, const uint32_t* n_dev,
-                                                         int passes, uint32_t* __restrict__ ctrl,
-                                                         uint32_t* __restrict__ digit_base) {
+                                                         int passes, uint32_t* __restrict__ ctrl) {
     constexpr int D = 1 << BITS;
     if (n_dev) n = (int64_t)*n_dev;   // coherent sort: the mover count is only known on the device
     __shared__ uint32_t h[OS_MAX_PASSES][D];
-    __shared__ bool last;
     for (int i = threadIdx.x; i < OS_MAX_PASSES * D; i += 256) (&h[0][0])[i] = 0;
     __syncthreads();
     // every thread owns 16 CONSECUTIVE keys: the keys are nearly sorted (physical order = last substep's order),
@@ -90,31 +88,6 @@ __global__ void __launch_bounds__(256) k_sort_digit_hist(const uint32_t* __restr
         const uint32_t v = h[p][d];
         if (v) atomicAdd(&ghist[p * 512 + d], v);
     }
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) last = (atomicAdd(&ctrl[4], 1u) == gridDim.x - 1);
-    __syncthreads();
-    if (!last) return;
-    __threadfence();
-    // the last block turns the histograms into exclusive digit bases (D <= 512, two digits per thread)
-    __shared__ uint32_t part[256];
-    for (int p = 0; p < passes; ++p) {
-        const volatile uint32_t* g = ghist + p * 512;
-        const uint32_t a = (2 * threadIdx.x < D) ? g[2 * threadIdx.x] : 0u;
-        const uint32_t b = (2 * threadIdx.x + 1 < D) ? g[2 * threadIdx.x + 1] : 0u;
-        part[threadIdx.x] = a + b;
-        __syncthreads();
-        for (int o = 1; o < 256; o <<= 1) {
-            const uint32_t v = (threadIdx.x >= o) ? part[threadIdx.x - o] : 0u;
-            __syncthreads();
-            part[threadIdx.x] += v;
-            __syncthreads();
-        }
-        const uint32_t ex = part[threadIdx.x] - (a + b);
-        if (2 * threadIdx.x < D) digit_base[p * 512 + 2 * threadIdx.x] = ex;
-        if (2 * threadIdx.x + 1 < D) digit_base[p * 512 + 2 * threadIdx.x + 1] = ex + a;
-        __syncthreads();
-    }
 }
 
 // CTA threads rank ROUNDS keys each: 256 x 16 for the full sort; 1024 x 4 for the coherent sort's few movers, where
@@ -125,7 +98,7 @@ __global__ void __launch_bounds__(CTA) k_sort_onesweep(const uint32_t* __restric
                                                                  uint32_t* __restrict__ keys_out,
                                                                  uint32_t* __restrict__ vals_out, int64_t n,
                                                                  const uint32_t* n_dev, int shift,
-                                                                 const uint32_t* __restrict__ digit_base,
+                                                                 const uint32_t* __restrict__ ghist,
                                                                  uint32_t* __restrict__ status, uint32_t* __restrict__ tile_counter) {
     constexpr int D = 1 << BITS;
     constexpr int CHUNK = CTA * ROUNDS;
@@ -139,13 +112,22 @@ __global__ void __launch_bounds__(CTA) k_sort_onesweep(const uint32_t* __restric
     uint32_t* sval = os_stage + CHUNK;
     uint32_t (*wh)[D] = reinterpret_cast<uint32_t (*)[D]>(os_stage + 2 * CHUNK);   // per-warp digit counters
     __shared__ uint32_t part[CTA];
+    __shared__ uint32_t parth[CTA];   // the global digit histogram rides along in the same scans -> exclusive digit bases
     __shared__ uint32_t tile_s;
-    if (n_dev) n = (int64_t)*n_dev;   // the grid is sized for the worst case; surplus CTAs leave at once
+    uint32_t hcount[DPT], hbase[DPT];
+#pragma unroll
+    for (int q = 0; q < DPT; ++q) { const int d = threadIdx.x + q * CTA; hcount[q] = d < D ? ghist[d] : 0u; hbase[q] = 0u; }
+    if (n_dev) n = (int64_t)*n_dev;   // coherent sort: the mover count is only known on the device
+    // tiles are handed out by ticket (so every tile a CTA waits for in the look-back is running or done); a CTA
+    // keeps taking tiles until none are left, which lets the coherent sort launch a small fixed grid
+    for (;;) {
+    __syncthreads();   // the previous tile's write-out is done with the staging area and tile_s
     if (threadIdx.x == 0) tile_s = atomicAdd(tile_counter, 1u);
-    for (int i = threadIdx.x; i < NW * D; i += CTA) (&wh[0][0])[i] = 0;
     __syncthreads();
     const uint32_t tile = tile_s;
     if ((int64_t)tile * CHUNK >= n) return;
+    for (int i = threadIdx.x; i < NW * D; i += CTA) (&wh[0][0])[i] = 0;
+    __syncthreads();
     const int w = threadIdx.x >> 5;
     const unsigned lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
@@ -212,26 +194,35 @@ __global__ void __launch_bounds__(CTA) k_sort_onesweep(const uint32_t* __restric
         for (int q = 0; q < DPT; ++q) s += total[q];
         // thread t holds digits t and t+CTA: scan in digit order needs two sweeps when DPT == 2
         part[threadIdx.x] = total[0];
+        parth[threadIdx.x] = hcount[0];
         __syncthreads();
         for (int o = 1; o < CTA; o <<= 1) {
             const uint32_t v = (threadIdx.x >= o) ? part[threadIdx.x - o] : 0u;
+            const uint32_t vh = (threadIdx.x >= o) ? parth[threadIdx.x - o] : 0u;
             __syncthreads();
             part[threadIdx.x] += v;
+            parth[threadIdx.x] += vh;
             __syncthreads();
         }
         const uint32_t lo_total = part[CTA - 1];  // count of digits [0, CTA)
+        const uint32_t lo_htotal = parth[CTA - 1];
         if (threadIdx.x < D) lstart[threadIdx.x] = part[threadIdx.x] - total[0];
+        hbase[0] = parth[threadIdx.x] - hcount[0];
         __syncthreads();
         if (DPT == 2) {
             part[threadIdx.x] = total[DPT - 1];
+            parth[threadIdx.x] = hcount[DPT - 1];
             __syncthreads();
             for (int o = 1; o < CTA; o <<= 1) {
                 const uint32_t v = (threadIdx.x >= o) ? part[threadIdx.x - o] : 0u;
+                const uint32_t vh = (threadIdx.x >= o) ? parth[threadIdx.x - o] : 0u;
                 __syncthreads();
                 part[threadIdx.x] += v;
+                parth[threadIdx.x] += vh;
                 __syncthreads();
             }
             if (threadIdx.x + CTA < D) lstart[threadIdx.x + CTA] = lo_total + part[threadIdx.x] - total[DPT - 1];
+            hbase[DPT - 1] = lo_htotal + parth[threadIdx.x] - hcount[DPT - 1];
             __syncthreads();
         }
         (void)s;
@@ -243,17 +234,27 @@ __global__ void __launch_bounds__(CTA) k_sort_onesweep(const uint32_t* __restric
         if (d < D) {
             uint32_t excl = 0;
             if (tile > 0) {
+                // walk back over the earlier tiles eight status words at a time (independent loads): with all tiles
+                // resident at once -- the coherent sort's few tiles -- a one-by-one walk is a chain of L2 round trips
                 int64_t t = (int64_t)tile - 1;
-                while (true) {
-                    const uint32_t v = *((volatile const uint32_t*)&status[(size_t)t * D + d]);
-                    if ((v & (OS_FLAG_AGG | OS_FLAG_INC)) == 0u) continue;  // that tile is still counting
-                    excl += v & OS_MASK;
-                    if (v & OS_FLAG_INC) break;
-                    --t;
+                bool done = false;
+                while (!done) {
+                    uint32_t v[8];
+#pragma unroll
+                    for (int b = 0; b < 8; ++b)
+                        v[b] = (t - b >= 0) ? *((volatile const uint32_t*)&status[(size_t)(t - b) * D + d]) : OS_FLAG_INC;
+                    int b = 0;
+#pragma unroll
+                    for (; b < 8; ++b) {
+                        if ((v[b] & (OS_FLAG_AGG | OS_FLAG_INC)) == 0u) break;   // that tile is still counting: reload from it
+                        excl += v[b] & OS_MASK;
+                        if (v[b] & OS_FLAG_INC) { done = true; break; }
+                    }
+                    t -= b;
                 }
                 atomicExch(&status[(size_t)tile * D + d], (excl + total[q]) | OS_FLAG_INC);
             }
-            gdelta[d] = digit_base[d] + excl - lstart[d];
+            gdelta[d] = hbase[q] + excl - lstart[d];
         }
     }
     __syncthreads();
@@ -289,6 +290,7 @@ __global__ void __launch_bounds__(CTA) k_sort_onesweep(const uint32_t* __restric
             vals_out[pos] = sval[i];
         }
     }
+    }   // next tile
 }
 
 
@@ -316,22 +318,34 @@ __global__ void __launch_bounds__(CTA) k_sort_onesweep(const uint32_t* __restric
 // Warp-parallel decoupled look-back: sum of the aggregates of chunks [0, chunk).  Chunks are handed out by ticket,
 // so every predecessor has at least started.
 __device__ __forceinline__ uint32_t cs_lookback(const uint32_t* status, uint32_t chunk, unsigned lane) {
+    // Window of 128 predecessors per step (lane l reads chunk-1-l, -33-l, -65-l, -97-l): with every chunk resident at
+    // once the walk and the front of inclusive prefixes approach each other 2 x 128 chunks per L2 round trip.
     uint32_t excl = 0;
     int64_t t = (int64_t)chunk - 1;
     while (t >= 0) {
-        const int64_t mine = t - (int64_t)lane;
-        uint32_t v;
+        uint32_t v[4];
         bool ready;
         do {
-            v = (mine >= 0) ? *((volatile const uint32_t*)&status[mine]) : OS_FLAG_INC;   // before chunk 0: prefix 0
-            ready = (v & (OS_FLAG_AGG | OS_FLAG_INC)) != 0u;
+            ready = true;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                const int64_t mine = t - 32 * g - (int64_t)lane;
+                v[g] = (mine >= 0) ? *((volatile const uint32_t*)&status[mine]) : OS_FLAG_INC;   // before chunk 0: prefix 0
+                ready = ready && ((v[g] & (OS_FLAG_AGG | OS_FLAG_INC)) != 0u);
+            }
         } while (!__all_sync(0xffffffffu, ready));
-        const unsigned inc = __ballot_sync(0xffffffffu, (v & OS_FLAG_INC) != 0u);
-        const int first = __ffs(inc) - 1;   // nearest predecessor holding an inclusive prefix (-1: none in this window)
-        const uint32_t c = (inc == 0u || (int)lane <= first) ? (v & OS_MASK) : 0u;
-        excl += __reduce_add_sync(0xffffffffu, c);
-        if (inc) break;
-        t -= 32;
+        bool found = false;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            if (found) break;
+            const unsigned inc = __ballot_sync(0xffffffffu, (v[g] & OS_FLAG_INC) != 0u);
+            const int first = __ffs(inc) - 1;   // nearest predecessor of this group holding an inclusive prefix
+            const uint32_t c = (inc == 0u || (int)lane <= first) ? (v[g] & OS_MASK) : 0u;
+            excl += __reduce_add_sync(0xffffffffu, c);
+            found = inc != 0u;
+        }
+        if (found) break;
+        t -= 128;
     }
     return excl;
 }
@@ -371,7 +385,7 @@ __global__ void __launch_bounds__(CS_THREADS) k_cs_flag_scan(const uint32_t* __r
                                                              uint32_t* __restrict__ mask, uint32_t* __restrict__ mprefix,
                                                              uint32_t* __restrict__ cnt, uint32_t* __restrict__ mk,
                                                              uint32_t* __restrict__ mv, int bits, int passes,
-                                                             uint32_t* __restrict__ digit_base) {
+                                                             uint32_t* __restrict__ samples) {
     __shared__ uint32_t chunk_s, excl_s;
     __shared__ uint32_t wsum[CS_THREADS / 32];
     if (threadIdx.x == 0) chunk_s = atomicAdd(&ctrl[CS_CTRL_TICKET_A], 1u);
@@ -383,18 +397,29 @@ __global__ void __launch_bounds__(CS_THREADS) k_cs_flag_scan(const uint32_t* __r
     const int64_t wbase = (int64_t)chunk * CS_CHUNK + (int64_t)w * 512;
     uint32_t k[16];
     uint32_t myword = 0;   // lane r < 16 keeps the mover mask of the warp's r-th word
+    {   // 1024 evenly spaced old keys, the first level of k_cs_place_movers' searches: this chunk's share
+        const uint32_t sstride = ((uint32_t)n + 1023u) / 1024u;
+        const int64_t c0 = (int64_t)chunk * CS_CHUNK, c1 = min(c0 + CS_CHUNK, n);
+        for (int64_t si = (c0 + sstride - 1) / sstride + threadIdx.x; si * sstride < c1; si += CS_THREADS) samples[si] = okeys[si * sstride];
+    }
+    uint32_t ok[16];
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {   // all 32 loads in flight before the first vote
+        const int64_t slot = wbase + r * 32 + lane;
+        k[r] = 0; ok[r] = 0;
+        if (slot < n) { k[r] = __ldg(keys + slot); ok[r] = __ldg(okeys + slot); }
+    }
 #pragma unroll
     for (int r = 0; r < 16; ++r) {
-        const int64_t slot = wbase + r * 32 + lane;
-        bool moved = false;
-        k[r] = 0;
-        if (slot < n) { k[r] = keys[slot]; moved = (k[r] != okeys[slot]); }
-        const unsigned m = __ballot_sync(0xffffffffu, moved);
+        const unsigned m = __ballot_sync(0xffffffffu, k[r] != ok[r]);
         if ((int)lane == r) myword = m;
     }
     const uint32_t pc = __popc(myword);
+    __shared__ uint32_t hist_s[OS_MAX_PASSES * 512];
+    for (int i = threadIdx.x; i < passes * 512; i += CS_THREADS) hist_s[i] = 0u;
     uint32_t total;
-    const uint32_t wordex = cs_chunk_scan(pc, chunk, status, wsum, &excl_s, &total);
+    const uint32_t wordex = cs_chunk_scan(pc, chunk, status, wsum, &excl_s, &total);   // (its barriers also publish hist_s = 0)
+    const uint32_t total_movers_cta = total - excl_s;
     if (threadIdx.x == 0 && (int64_t)(chunk + 1) * CS_CHUNK >= n) ctrl[CS_CTRL_MOVERS] = total;
     const int64_t word0 = wbase >> 5;
     if (lane < 16 && (word0 + lane) * 32 < n) {
@@ -410,36 +435,17 @@ __global__ void __launch_bounds__(CS_THREADS) k_cs_flag_scan(const uint32_t* __r
             const uint32_t c = ex + __popc(m & lt);
             mk[c] = k[r];
             mv[c] = (uint32_t)(wbase + r * 32 + lane);
-            // digit histograms of the movers for every radix pass (few movers: straight to the global table)
-            for (int p = 0; p < passes; ++p) atomicAdd(&ctrl[OS_CTRL_HIST + p * 512 + ((k[r] >> (p * bits)) & ((1u << bits) - 1u))], 1u);
+            // digit histograms of the movers for every radix pass, aggregated per CTA (a chunk's movers share
+            // their high digits)
+            for (int p = 0; p < passes; ++p) atomicAdd(&hist_s[p * 512 + ((k[r] >> (p * bits)) & ((1u << bits) - 1u))], 1u);
         }
     }
-    // the last CTA to finish turns the histograms into exclusive digit bases (as k_sort_digit_hist does)
-    __shared__ bool last;
-    __shared__ uint32_t part[CS_THREADS];
-    __threadfence();
     __syncthreads();
-    if (threadIdx.x == 0) last = (atomicAdd(&ctrl[4], 1u) == gridDim.x - 1);
-    __syncthreads();
-    if (!last) return;
-    __threadfence();
-    const int D = 1 << bits;
-    for (int p = 0; p < passes; ++p) {
-        const volatile uint32_t* g = ctrl + OS_CTRL_HIST + p * 512;
-        const uint32_t a = (2 * (int)threadIdx.x < D) ? g[2 * threadIdx.x] : 0u;
-        const uint32_t b = (2 * (int)threadIdx.x + 1 < D) ? g[2 * threadIdx.x + 1] : 0u;
-        part[threadIdx.x] = a + b;
-        __syncthreads();
-        for (int o = 1; o < CS_THREADS; o <<= 1) {
-            const uint32_t v = ((int)threadIdx.x >= o) ? part[threadIdx.x - o] : 0u;
-            __syncthreads();
-            part[threadIdx.x] += v;
-            __syncthreads();
+    if (total_movers_cta) {
+        for (int i = threadIdx.x; i < passes * 512; i += CS_THREADS) {
+            const uint32_t v = hist_s[i];
+            if (v) atomicAdd(&ctrl[OS_CTRL_HIST + i], v);
         }
-        const uint32_t ex = part[threadIdx.x] - (a + b);
-        if (2 * (int)threadIdx.x < D) digit_base[p * 512 + 2 * threadIdx.x] = ex;
-        if (2 * (int)threadIdx.x + 1 < D) digit_base[p * 512 + 2 * threadIdx.x + 1] = ex + a;
-        __syncthreads();
     }
 }
 
@@ -448,7 +454,7 @@ __global__ void __launch_bounds__(256) k_cs_place_movers(const uint32_t* __restr
                                                          int64_t n, const uint32_t* __restrict__ mask,
                                                          const uint32_t* __restrict__ mprefix, uint32_t* __restrict__ cnt,
                                                          uint32_t* __restrict__ mx, uint32_t* __restrict__ out_keys,
-                                                         uint32_t* __restrict__ out_perm) {
+                                                         uint32_t* __restrict__ out_perm, const uint32_t* __restrict__ samples) {
     const uint32_t M = ctrl[CS_CTRL_MOVERS];
     const uint32_t N = (uint32_t)n;
     // first level of the searches: 1024 evenly spaced old keys in shared memory
@@ -456,7 +462,7 @@ __global__ void __launch_bounds__(256) k_cs_place_movers(const uint32_t* __restr
     const uint32_t stride = (N + 1023u) / 1024u;
     for (uint32_t i = threadIdx.x; i < 1024u; i += blockDim.x) {
         const uint64_t idx = (uint64_t)i * stride;
-        samp[i] = idx < N ? okeys[idx] : 0xffffffffu;
+        samp[i] = idx < N ? samples[i] : 0xffffffffu;
     }
     __syncthreads();
     for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < M; t += gridDim.x * blockDim.x) {
@@ -475,6 +481,18 @@ __global__ void __launch_bounds__(256) k_cs_place_movers(const uint32_t* __restr
         hi = whi < N ? (uint32_t)whi : N;
         lo = lo ? (lo - 1u) * stride + 1u : 0u;
         if (up) lo = max(lo, j + 1u); else hi = min(hi, j);
+        // 4-ary search: three independent probes per step halve the chain of dependent loads
+        while (hi - lo > 2u) {
+            const uint32_t q = (hi - lo) >> 2;
+            const uint32_t m1 = lo + q, m2 = lo + 2u * q, m3 = lo + 3u * q;
+            const uint32_t v1 = okeys[m1], v2 = okeys[m2], v3 = okeys[m3];
+            const bool b1 = up ? (v1 < kj) : (v1 <= kj), b2 = up ? (v2 < kj) : (v2 <= kj), b3 = up ? (v3 < kj) : (v3 <= kj);
+            // the predicate is monotone (true ... true false ... false): the answer is the first false position
+            if (!b1) hi = m1;
+            else if (!b2) { lo = m1 + 1u; hi = m2; }
+            else if (!b3) { lo = m2 + 1u; hi = m3; }
+            else lo = m3 + 1u;
+        }
         while (lo < hi) {
             const uint32_t mid = (lo + hi) >> 1;
             const uint32_t v = okeys[mid];
@@ -551,7 +569,7 @@ static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     const uint32_t* keys = (const uint32_t*)ctx->b.keys;
     const int first = passes & 1;   // the compacted movers start in this buffer so that the last radix pass lands in buffer 0
     k_cs_flag_scan<<<ntiles, CS_THREADS, 0, s>>>(keys, okeys, ctx->n, ctrl, status_a, ctx->cs_mask, ctx->cs_mprefix, ctx->cs_cnt,
-                                                 ctx->cs_mk[first], ctx->cs_mv[first], BITS, passes, ctx->hist_tot);
+                                                 ctx->cs_mk[first], ctx->cs_mv[first], BITS, passes, ctx->hist_tot);   // hist_tot: 1024 key samples
     MPMK_LAUNCH_CHECK(ctx);
     const uint32_t* m_dev = ctrl + CS_CTRL_MOVERS;
     constexpr int stage_bytes = 2 * MPMK_SORT_CHUNK * 4 + (1024 / 32) * D * 4;   // staging + per-warp digit counters
@@ -561,10 +579,11 @@ static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s) {
         attr_set = true;
     }
     int in = first;
+    const int mgrid = ntiles < ctx->sm_count ? ntiles : ctx->sm_count;   // persistent: CTAs loop over the movers' tiles
     for (int p = 0; p < passes; ++p) {
         const int o = 1 - in;
-        k_sort_onesweep<BITS, 1024, 4><<<ntiles, 1024, stage_bytes, s>>>(ctx->cs_mk[in], ctx->cs_mv[in], ctx->cs_mk[o], ctx->cs_mv[o], 0, m_dev,
-                                                               p * BITS, ctx->hist_tot + p * 512,
+        k_sort_onesweep<BITS, 1024, 4><<<mgrid, 1024, stage_bytes, s>>>(ctx->cs_mk[in], ctx->cs_mv[in], ctx->cs_mk[o], ctx->cs_mv[o], 0, m_dev,
+                                                               p * BITS, ctx->sort_ctrl + OS_CTRL_HIST + p * 512,
                                                                ctrl + OS_CTRL_STATUS + (size_t)p * ntiles * D, ctrl + p);
         MPMK_LAUNCH_CHECK(ctx);
         in = o;
@@ -572,7 +591,7 @@ static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     // sorted movers are in buffer `in` (== 0); the other key buffer is free and receives x_t
     uint32_t* mx = ctx->cs_mk[1 - in];
     k_cs_place_movers<<<ctx->sm_count * 4, 256, 0, s>>>(ctx->cs_mk[in], ctx->cs_mv[in], ctrl, okeys, ctx->n, ctx->cs_mask, ctx->cs_mprefix,
-                                                        ctx->cs_cnt, mx, ctx->keys_alt, ctx->perm);
+                                                        ctx->cs_cnt, mx, ctx->keys_alt, ctx->perm, ctx->hist_tot);
     MPMK_LAUNCH_CHECK(ctx);
     k_cs_place_stayers<<<ntiles, CS_THREADS, 0, s>>>(keys, ctx->n, ctrl, status_b, ctx->cs_mask, ctx->cs_mprefix, ctx->cs_cnt, mx,
                                                      ctx->keys_alt, ctx->perm);
@@ -591,7 +610,7 @@ static int sort_all(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     const size_t ctrl_words = OS_CTRL_STATUS + (size_t)passes * ntiles * D;
     MPMK_CHECK(ctx, cudaMemsetAsync(ctx->sort_ctrl, 0, ctrl_words * 4, s));
     int hgrid = ntiles < ctx->sm_count * 4 ? ntiles : ctx->sm_count * 4;
-    k_sort_digit_hist<BITS><<<hgrid, 256, 0, s>>>((const uint32_t*)ctx->b.keys, ctx->n, nullptr, passes, ctx->sort_ctrl, ctx->hist_tot);
+    k_sort_digit_hist<BITS><<<hgrid, 256, 0, s>>>((const uint32_t*)ctx->b.keys, ctx->n, nullptr, passes, ctx->sort_ctrl);
     MPMK_LAUNCH_CHECK(ctx);
     uint32_t* kb[2] = {ctx->sorted_keys, ctx->keys_alt};
     uint32_t* vb[2] = {ctx->perm, ctx->perm_alt};
@@ -605,7 +624,7 @@ static int sort_all(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     }
     for (int p = 0; p < passes; ++p) {
         const int o = (passes - 1 - p) & 1;
-        k_sort_onesweep<BITS, 256, 16><<<ntiles, 256, stage_bytes, s>>>(kin, vin, kb[o], vb[o], ctx->n, nullptr, p * BITS, ctx->hist_tot + p * 512,
+        k_sort_onesweep<BITS, 256, 16><<<ntiles, 256, stage_bytes, s>>>(kin, vin, kb[o], vb[o], ctx->n, nullptr, p * BITS, ctx->sort_ctrl + OS_CTRL_HIST + p * 512,
                                                                ctx->sort_ctrl + OS_CTRL_STATUS + (size_t)p * ntiles * D,
                                                                ctx->sort_ctrl + p);
         MPMK_LAUNCH_CHECK(ctx);
