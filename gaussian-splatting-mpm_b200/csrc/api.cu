@@ -57,6 +57,7 @@ static int create_impl(mpmk_ctx* ctx, int device, int n_grid, double grid_extent
     MPMK_CHECK(ctx, cudaStreamCreateWithFlags(&ctx->cap_stream, cudaStreamNonBlocking));
     { int rc = mpmk_p2g_init(ctx); if (rc) return rc; }
     { int rc = mpmk_g2p_init(ctx); if (rc) return rc; }
+    { int rc = mpmk_g2p2g_init(ctx); if (rc) return rc; }
     ctx->prm.alpha = 0.0f;
     return 0;
 }
@@ -183,6 +184,31 @@ extern "C" int mpmk_substep(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops
     return substep_impl(ctx, dt, ops, (cudaStream_t)stream);
 }
 
+// n >= 1 substeps of constant dt and ops.  With MPMK_FUSE_G2P2G and two or more substeps (single GPU) only the first
+// scatter and the last gather run as stand-alone kernels; in between, the gather of substep i and the scatter of substep i+1 are one kernel
+// (g2p2g.cu).  F_trial is only consumed by export: it is stored by the last g2p of the batch.
+static int substeps_impl(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, int n_steps, cudaStream_t s) {
+    const uint32_t user_flags = ctx->prm.flags;
+    const bool fuse = n_steps >= 2 && !ctx->mg.enabled && (user_flags & MPMK_FUSE_G2P2G);
+    int rc = 0;
+    for (int i = 0; i < n_steps && rc == 0; ++i) {
+        const bool last = (i == n_steps - 1);
+        ctx->prm.flags = last ? user_flags : (user_flags & ~MPMK_WRITE_FTRIAL);
+        if (!fuse) { rc = substep_impl(ctx, dt, ops, s); continue; }
+        ctx->keep_grid_in = (i > 0);    // the previous fused kernel already scattered this substep into grid_in
+        ctx->zero_grid_in = !last;      // ... and the next one needs grid_in zero where this substep touched it
+        if ((rc = mpmk_launch_sort(ctx, s))) break;
+        if ((rc = mpmk_launch_prepare(ctx, s))) break;
+        if (i == 0 && (rc = mpmk_launch_p2g(ctx, dt, ops, s))) break;
+        if ((rc = mpmk_launch_grid(ctx, dt, ops, s))) break;
+        rc = last ? mpmk_launch_g2p(ctx, dt, s) : mpmk_launch_g2p2g(ctx, dt, ops, s);
+    }
+    ctx->keep_grid_in = false;
+    ctx->zero_grid_in = false;
+    ctx->prm.flags = user_flags;
+    return rc;
+}
+
 static bool same_bindings(const mpmk_bindings& a, const mpmk_bindings& b) { return memcmp(&a, &b, sizeof(a)) == 0; }
 
 extern "C" int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, int n_steps, void* stream) {
@@ -196,13 +222,7 @@ extern "C" int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* op
     if (ctx->mg.enabled) {
         // slab mode: the substeps carry ncclSend/ncclRecv; they are issued eagerly on the caller's stream
         // (no host synchronisation in between), not captured
-        int rc = 0;
-        for (int i = 0; i < n_steps && rc == 0; ++i) {
-            ctx->prm.flags = (i == n_steps - 1) ? user_flags : (user_flags & ~MPMK_WRITE_FTRIAL);
-            rc = substep_impl(ctx, dt, ops, s);
-        }
-        ctx->prm.flags = user_flags;
-        return rc;
+        return substeps_impl(ctx, dt, ops, n_steps, s);
     }
     // look for a captured graph with identical launch parameters
     for (int i = 0; i < ctx->n_graphs; ++i) {
@@ -232,13 +252,7 @@ extern "C" int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* op
     const int64_t launches_before = ctx->launches;
     cudaStream_t cs = ctx->cap_stream;
     MPMK_CHECK(ctx, cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
-    int rc = 0;
-    for (int i = 0; i < n_steps && rc == 0; ++i) {
-        // F_trial is only consumed by export: store it on the last substep of the batch only
-        ctx->prm.flags = (i == n_steps - 1) ? user_flags : (user_flags & ~MPMK_WRITE_FTRIAL);
-        rc = substep_impl(ctx, dt, ops, cs);
-    }
-    ctx->prm.flags = user_flags;
+    const int rc = substeps_impl(ctx, dt, ops, n_steps, cs);
     cudaGraph_t graph = nullptr;
     cudaError_t ce = cudaStreamEndCapture(cs, &graph);
     if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }

@@ -10,11 +10,12 @@ struct GridOpsArg {
     mpmk_grid_op ops[MPMK_MAX_GRID_OPS];
 };
 
-__device__ __forceinline__ void grid_node_update(const float4* __restrict__ gin, float4* __restrict__ gout, int ix, int iy,
+__device__ __forceinline__ void grid_node_update(float4* __restrict__ gin, float4* __restrict__ gout, int ix, int iy,
                                                  int iz, int n, float dx, float dt, float gx, float gy, float gz,
-                                                 const GridOpsArg& ops) {
+                                                 const GridOpsArg& ops, int zero_in) {
     size_t node = ((size_t)ix * n + iy) * n + iz;
     float4 m = gin[node];
+    if (zero_in) gin[node] = make_float4(0.f, 0.f, 0.f, 0.f);   // fused batches: ready for the next substep's scatter
     float vx = 0.f, vy = 0.f, vz = 0.f;
     if (m.w > 1e-15f) {
         vx = __fdiv_rn(m.x, m.w) + dt * gx;
@@ -52,10 +53,10 @@ __device__ __forceinline__ void grid_node_update(const float4* __restrict__ gin,
     gout[node] = make_float4(vx, vy, vz, 0.f);
 }
 
-__global__ void __launch_bounds__(256) k_grid(const float4* __restrict__ gin, float4* __restrict__ gout,
+__global__ void __launch_bounds__(256) k_grid(float4* __restrict__ gin, float4* __restrict__ gout,
                                               const uint32_t* __restrict__ list, const uint32_t* __restrict__ count,
                                               int n, int nb, float dx, float dt, float gx, float gy, float gz,
-                                              const GridOpsArg ops) {
+                                              const GridOpsArg ops, int zero_in) {
     const int64_t total = (int64_t)(*count) * 64;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         uint32_t b = list[i >> 6];
@@ -63,12 +64,12 @@ __global__ void __launch_bounds__(256) k_grid(const float4* __restrict__ gin, fl
         int bz = b % nb, by = (b / nb) % nb, bx = b / (nb * nb);
         int ix = 4 * bx + (l >> 4), iy = 4 * by + ((l >> 2) & 3), iz = 4 * bz + (l & 3);
         if (ix >= n || iy >= n || iz >= n) continue;
-        grid_node_update(gin, gout, ix, iy, iz, n, dx, dt, gx, gy, gz, ops);
+        grid_node_update(gin, gout, ix, iy, iz, n, dx, dt, gx, gy, gz, ops, zero_in);
     }
 }
 
 // multi-GPU: the same update, densely over the planes [x0, x1) shared with a neighbouring slab (mg.cu)
-__global__ void __launch_bounds__(256) k_grid_planes(const float4* __restrict__ gin, float4* __restrict__ gout, int x0, int x1,
+__global__ void __launch_bounds__(256) k_grid_planes(float4* __restrict__ gin, float4* __restrict__ gout, int x0, int x1,
                                                      int y0, int y1, int n, float dx, float dt, float gx, float gy, float gz,
                                                      const GridOpsArg ops) {
     const int64_t per_plane = (int64_t)(y1 - y0) * n, total = per_plane * (x1 - x0);
@@ -76,7 +77,7 @@ __global__ void __launch_bounds__(256) k_grid_planes(const float4* __restrict__ 
         const int ix = x0 + (int)(i / per_plane);
         const int64_t rem = i % per_plane;
         const int iy = y0 + (int)(rem / n), iz = (int)(rem % n);
-        grid_node_update(gin, gout, ix, iy, iz, n, dx, dt, gx, gy, gz, ops);
+        grid_node_update(gin, gout, ix, iy, iz, n, dx, dt, gx, gy, gz, ops, 0);
     }
 }
 
@@ -89,17 +90,17 @@ int mpmk_launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaS
         a.n_ops = ops->n_ops;
         memcpy(a.ops, ops->ops, sizeof(mpmk_grid_op) * ops->n_ops);
     }
-    k_grid<<<ctx->sm_count * 8, 256, 0, s>>>((const float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out,
+    k_grid<<<ctx->sm_count * 8, 256, 0, s>>>((float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out,
                                              ctx->block_list[ctx->cur_list], ctx->block_count[ctx->cur_list],
                                              ctx->n_grid, ctx->nb, ctx->dx, dt, ctx->prm.gravity[0], ctx->prm.gravity[1],
-                                             ctx->prm.gravity[2], a);
+                                             ctx->prm.gravity[2], a, ctx->zero_grid_in ? 1 : 0);
     MPMK_LAUNCH_CHECK(ctx);
     if (ctx->mg.enabled) {
         const MgState& m = ctx->mg;
         const int r0[2] = {m.lo0, m.hi0}, r1[2] = {m.lo1, m.hi1};
         for (int k = 0; k < 2; ++k) {
             if (r1[k] <= r0[k]) continue;
-            k_grid_planes<<<ctx->sm_count * 4, 256, 0, s>>>((const float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out, r0[k], r1[k],
+            k_grid_planes<<<ctx->sm_count * 4, 256, 0, s>>>((float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out, r0[k], r1[k],
                                                             m.y_lo, m.y_hi, ctx->n_grid, ctx->dx, dt, ctx->prm.gravity[0], ctx->prm.gravity[1],
                                                             ctx->prm.gravity[2], a);
             MPMK_LAUNCH_CHECK(ctx);

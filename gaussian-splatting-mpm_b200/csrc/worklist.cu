@@ -8,7 +8,7 @@
 
 __global__ void k_clear_blocks(float4* __restrict__ gin, float4* __restrict__ gout, const uint32_t* __restrict__ list,
                                const uint32_t* __restrict__ count, int n, int nb, uint32_t* stamp, DevCounters* cnt,
-                               uint32_t* next_count) {
+                               uint32_t* next_count, int clear_in) {
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         *stamp += 1u;  // consumed by k_build_items (a later launch on the stream)
         // this substep's counters / block list start empty (the previous substep's kernels are done with them)
@@ -25,7 +25,7 @@ __global__ void k_clear_blocks(float4* __restrict__ gin, float4* __restrict__ go
         int ix = 4 * bx + (l >> 4), iy = 4 * by + ((l >> 2) & 3), iz = 4 * bz + (l & 3);
         if (ix < n && iy < n && iz < n) {
             size_t node = ((size_t)ix * n + iy) * n + iz;
-            gin[node] = z;
+            if (clear_in) gin[node] = z;   // fused batches: grid_in already holds this substep's scatter
             gout[node] = z;
         }
     }
@@ -94,7 +94,7 @@ int mpmk_launch_prepare(mpmk_ctx* ctx, cudaStream_t s) {
     // clear what the previous substep touched; reset the per-substep counters
     k_clear_blocks<<<ctx->sm_count * 8, 256, 0, s>>>((float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out,
                                                      ctx->block_list[prev], ctx->block_count[prev], ctx->n_grid, ctx->nb,
-                                                     ctx->dev_stamp, ctx->counters, ctx->block_count[next]);
+                                                     ctx->dev_stamp, ctx->counters, ctx->block_count[next], ctx->keep_grid_in ? 0 : 1);
     MPMK_LAUNCH_CHECK(ctx);
     if (ctx->mg.enabled) { int rc = mpmk_mg_clear_shared(ctx, s); if (rc) return rc; }
     if (ctx->n > 0) {

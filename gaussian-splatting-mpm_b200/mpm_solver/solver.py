@@ -65,6 +65,7 @@ class MPM_Simulator:
         self._strict_q3 = strict_q3
         self._track_cov = track_cov
         self._sort_full = False
+        self._fuse_g2p2g = False
         self._sync_flags()
 
     def load_particles(self, xyzs, covs, volumes):
@@ -97,6 +98,8 @@ class MPM_Simulator:
             f |= _native.TRACK_COV
         if self._sort_full:
             f |= _native.SORT_FULL
+        if self._fuse_g2p2g:
+            f |= _native.FUSE_G2P2G
         if self._has_plastic():
             f |= _native.WRITE_FTRIAL  # F_trial != F after a return mapping; export needs F_trial
         self._backend.params.flags = f
@@ -105,7 +108,8 @@ class MPM_Simulator:
     def set_parameters(self, params=None, **kw):
         """Update solver parameters from a dict (not in the reference; north_star asks for it).
         Keys: gravity, E, nu, yield_stress, hardening, xi, plastic_viscosity, softening, friction_angle,
-        strict_q1, strict_q3, track_cov, sort_full (always the full radix sort, never the merge of the movers)."""
+        strict_q1, strict_q3, track_cov, sort_full (always the full radix sort, never the merge of the movers), fuse_g2p2g (step() runs the gather of one
+        substep and the scatter of the next as one kernel)."""
         p = dict(params or {})
         p.update(kw)
         m = self.mpm_model
@@ -124,7 +128,7 @@ class MPM_Simulator:
                 m._logE.fill_(math.log10(v))
             elif k == "nu":
                 m._y.fill_(-math.log(0.49 / v - 1))
-            elif k in ("strict_q1", "strict_q3", "track_cov", "sort_full"):
+            elif k in ("strict_q1", "strict_q3", "track_cov", "sort_full", "fuse_g2p2g"):
                 setattr(self, "_" + k, bool(v))
             else:
                 raise KeyError(k)
