@@ -26,7 +26,7 @@ for p in (ROOT, PKG):
     if p not in sys.path:
         sys.path.insert(0, p)
 
-SUBSTEPS_PER_STEP = 10
+SUBSTEPS_PER_STEP = 100   # one frame of configs/lego.json / metal_cupnoodle.json: frame_dt 1e-2 / substep_dt 1e-4 (main.py:305-306)
 METRIC = "particle_substeps_per_sec"
 UNIT = "particle-substeps/s"
 
@@ -341,7 +341,7 @@ def main():
     sops = sim._ops_at(sim.time)
     stages = ["sort", "prepare", "p2g", "grid", "g2p"]
     acc = {k: 0.0 for k in stages}
-    reps = max(10, S)
+    reps = 20
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(6)] for _ in range(reps)]
     sp = stream.cuda_stream
     for r in range(reps):
@@ -411,9 +411,10 @@ def main():
 
     cpu = None
     if not a.no_cpu_baseline:
-        v, secs, cores = _cpu_reference(cloud, args, ops, substeps=2)
+        cpu_sub = 24
+        v, secs, cores = _cpu_reference(cloud, args, ops, substeps=cpu_sub)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": f"full {name} cloud ({n} particles, dense {args.n_grid}^3 grid), 2 substeps after 1 warm-up, {secs:.1f} s"}
+               "sample": f"full {name} cloud ({n} particles, dense {args.n_grid}^3 grid), {cpu_sub} substeps after 1 warm-up, {secs:.1f} s"}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",

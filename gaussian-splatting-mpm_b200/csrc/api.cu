@@ -263,10 +263,10 @@ extern "C" int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* op
     MPMK_CHECK(ctx, ce);
     e.exec = exec;
     e.end_coherent = ctx->coherent; e.end_last_sort_coherent = ctx->last_sort_coherent; e.end_sorted_keys = ctx->sorted_keys; e.end_keys_alt = ctx->keys_alt;
-    if (ctx->n_graphs == 4) {  // evict the oldest
+    if (ctx->n_graphs == MPMK_GRAPH_CACHE) {  // evict the oldest
         cudaGraphExecDestroy(ctx->graphs[0].exec);
-        for (int i = 1; i < 4; ++i) ctx->graphs[i - 1] = ctx->graphs[i];
-        ctx->n_graphs = 3;
+        for (int i = 1; i < MPMK_GRAPH_CACHE; ++i) ctx->graphs[i - 1] = ctx->graphs[i];
+        ctx->n_graphs = MPMK_GRAPH_CACHE - 1;
     }
     ctx->graphs[ctx->n_graphs++] = e;
     ctx->launches = launches_before;  // captured launches did not run; the replay below is what executes

@@ -22,6 +22,7 @@
 #endif
 #define MPMK_SORT_CHUNK (MPMK_SORT_CTA * MPMK_SORT_ROUNDS)
 #define MPMK_MAX_RADIX_BITS 9
+#define MPMK_GRAPH_CACHE 8          // captured substep batches kept per context
 
 struct DevCounters {
     uint32_t n_items;
@@ -110,7 +111,7 @@ struct mpmk_ctx {
         bool end_last_sort_coherent;
         uint32_t* end_sorted_keys;
         uint32_t* end_keys_alt;
-    } graphs[4];
+    } graphs[MPMK_GRAPH_CACHE];
     int n_graphs;
     cudaStream_t cap_stream;  // graphs are captured here (the legacy default stream cannot be captured)
     MgState mg;

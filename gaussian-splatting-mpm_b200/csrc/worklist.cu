@@ -35,13 +35,31 @@ __global__ void k_clear_blocks(float4* __restrict__ gin, float4* __restrict__ go
 // list, the last one records the run's end in the tile-indexed table (no search, no dependent loads)
 __global__ void __launch_bounds__(256) k_tile_runs(const uint32_t* __restrict__ skeys, int64_t n, uint2* __restrict__ tile_list,
                                                    uint32_t* __restrict__ tile_end, DevCounters* cnt) {
-    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= n) return;
-    const uint32_t tile = skeys[r] >> 6;
-    const uint32_t prev = r > 0 ? (skeys[r - 1] >> 6) : 0xffffffffu;
-    const uint32_t next = r + 1 < n ? (skeys[r + 1] >> 6) : 0xffffffffu;
-    if (tile != prev) tile_list[atomicAdd(&cnt->n_tiles, 1u)] = make_uint2(tile, (uint32_t)r);
-    if (tile != next) tile_end[tile] = (uint32_t)r + 1u;
+    // four consecutive keys per thread (one 16-byte load); the neighbours' edge keys come through shuffles, only the
+    // warp's two outer lanes touch memory again
+    const unsigned lane = threadIdx.x & 31;
+    for (int64_t r0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; r0 - 4 * (int64_t)lane < n; r0 += (int64_t)gridDim.x * blockDim.x * 4) {
+        uint32_t t[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+        if (r0 + 4 <= n) {
+            const uint4 v = *reinterpret_cast<const uint4*>(skeys + r0);
+            t[0] = v.x >> 6; t[1] = v.y >> 6; t[2] = v.z >> 6; t[3] = v.w >> 6;
+        } else {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) if (r0 + q < n) t[q] = skeys[r0 + q] >> 6;
+        }
+        uint32_t prev = __shfl_up_sync(0xffffffffu, t[3], 1);
+        uint32_t next = __shfl_down_sync(0xffffffffu, t[0], 1);
+        if (lane == 0) prev = (r0 > 0 && r0 - 1 < n) ? (skeys[r0 - 1] >> 6) : 0xffffffffu;
+        if (lane == 31) next = (r0 + 4 < n) ? (skeys[r0 + 4] >> 6) : 0xffffffffu;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            if (r0 + q >= n) break;
+            const uint32_t p = q ? t[q - 1] : prev;
+            const uint32_t nx = q < 3 ? t[q + 1] : next;
+            if (t[q] != p) tile_list[atomicAdd(&cnt->n_tiles, 1u)] = make_uint2(t[q], (uint32_t)(r0 + q));
+            if (t[q] != nx) tile_end[t[q]] = (uint32_t)(r0 + q) + 1u;
+        }
+    }
 }
 
 // pass 2 over the non-empty tiles: work items (chunks of <= MPMK_ITEM_MAX particles) and the node blocks
@@ -98,7 +116,7 @@ int mpmk_launch_prepare(mpmk_ctx* ctx, cudaStream_t s) {
     MPMK_LAUNCH_CHECK(ctx);
     if (ctx->mg.enabled) { int rc = mpmk_mg_clear_shared(ctx, s); if (rc) return rc; }
     if (ctx->n > 0) {
-        k_tile_runs<<<div_up(ctx->n, 256), 256, 0, s>>>(ctx->sorted_keys, ctx->n, ctx->tile_list, ctx->tile_end, ctx->counters);
+        k_tile_runs<<<min(div_up(ctx->n, 1024), ctx->sm_count * 8), 256, 0, s>>>(ctx->sorted_keys, ctx->n, ctx->tile_list, ctx->tile_end, ctx->counters);
         MPMK_LAUNCH_CHECK(ctx);
         k_build_items<<<ctx->sm_count, 256, 0, s>>>(ctx->tile_list, ctx->tile_end, ctx->items, ctx->counters, ctx->block_stamp,
                                                     ctx->dev_stamp, ctx->block_list[next], ctx->block_count[next], ctx->nt,
