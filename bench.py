@@ -243,7 +243,7 @@ def run_multi(a, rank, world, local, dev):
                            "substeps_per_step": S, "substep_dt": dt, "ghost_planes": 2,
                            "migration": f"every {sl.migrate_every} substeps (auto: half the ghost margin at the measured max speed)",
                            "l2": "particle state >> 126 MB L2 per GPU: inputs larger than L2, no flush needed",
-                           "parallelism": f"slab{world} (x-slabs, NCCL halo sum per substep, P2P migration)"},
+                           "parallelism": f"slab{world} (x-slabs, per-substep halo sum: " + ("stores into the neighbour's memory over NVLink + flags, no collective" if sl.halo_path == "peer" else "ncclSend/ncclRecv") + "; NCCL P2P migration)"},
                 "roofline": {"bound": "hbm", "kernel": "substep (all kernels, per GPU)", "achieved": ach, "peak": peak, "unit": "GB/s",
                              "frac": ach / peak, "traffic": None, "peak_source": peak_src,
                              "algorithmic_bytes_per_launch": sub_bytes / world,

@@ -85,7 +85,7 @@ extern "C" int mpmk_destroy(mpmk_ctx* ctx) {
     return 0;
 }
 
-static void drop_graphs(mpmk_ctx* ctx) {
+void mpmk_drop_graphs(mpmk_ctx* ctx) {
     for (int i = 0; i < ctx->n_graphs; ++i) cudaGraphExecDestroy(ctx->graphs[i].exec);
     ctx->n_graphs = 0;
 }
@@ -104,7 +104,7 @@ extern "C" int mpmk_bind(mpmk_ctx* ctx, const mpmk_bindings* b) {
     ctx->sorted_valid = false;
     ctx->prepared = false;
     ctx->ftrial_valid = false;
-    drop_graphs(ctx);
+    mpmk_drop_graphs(ctx);
     return 0;
 }
 
@@ -211,19 +211,9 @@ static int substeps_impl(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, i
 
 static bool same_bindings(const mpmk_bindings& a, const mpmk_bindings& b) { return memcmp(&a, &b, sizeof(a)) == 0; }
 
-extern "C" int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, int n_steps, void* stream) {
-    REQUIRE_BOUND(ctx);
-    if (n_steps <= 0) return 0;
-    cudaStream_t s = (cudaStream_t)stream;
-    mpmk_substep_ops zero_ops;
-    memset(&zero_ops, 0, sizeof(zero_ops));
-    if (!ops) ops = &zero_ops;
+// find or capture the CUDA graph of n_steps substeps from the current context state, and replay it
+static int graph_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, int n_steps, cudaStream_t s) {
     const uint32_t user_flags = ctx->prm.flags;
-    if (ctx->mg.enabled) {
-        // slab mode: the substeps carry ncclSend/ncclRecv; they are issued eagerly on the caller's stream
-        // (no host synchronisation in between), not captured
-        return substeps_impl(ctx, dt, ops, n_steps, s);
-    }
     // look for a captured graph with identical launch parameters
     for (int i = 0; i < ctx->n_graphs; ++i) {
         mpmk_ctx::GraphEntry& g = ctx->graphs[i];
@@ -231,7 +221,7 @@ extern "C" int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* op
             g.n == ctx->n && g.coherent == ctx->coherent && g.sorted_keys == ctx->sorted_keys &&
             memcmp(&g.ops, ops, sizeof(*ops)) == 0 && same_bindings(g.b, ctx->b)) {
             MPMK_CHECK(ctx, cudaGraphLaunch(g.exec, s));
-            ctx->launches += 1;
+            ctx->launches += g.kernels;
             ctx->coherent = g.end_coherent;
             ctx->last_sort_coherent = g.end_last_sort_coherent;
             ctx->sorted_keys = g.end_sorted_keys;
@@ -269,9 +259,8 @@ extern "C" int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* op
         ctx->n_graphs = MPMK_GRAPH_CACHE - 1;
     }
     ctx->graphs[ctx->n_graphs++] = e;
-    ctx->launches = launches_before;  // captured launches did not run; the replay below is what executes
+    ctx->graphs[ctx->n_graphs - 1].kernels = ctx->launches - launches_before;   // kernels one replay executes
     MPMK_CHECK(ctx, cudaGraphLaunch(exec, s));
-    ctx->launches += 1;
     ctx->ftrial_valid = (user_flags & MPMK_WRITE_FTRIAL) != 0;
     return 0;
 }
@@ -290,4 +279,39 @@ extern "C" int mpmk_read_counters(mpmk_ctx* ctx, mpmk_counters* out, void* strea
     out->n_tiles = h.n_tiles;
     out->n_clamped = h.n_clamped;
     return 0;
+}
+
+extern "C" int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, int n_steps, void* stream) {
+    REQUIRE_BOUND(ctx);
+    if (n_steps <= 0) return 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    mpmk_substep_ops zero_ops;
+    memset(&zero_ops, 0, sizeof(zero_ops));
+    if (!ops) ops = &zero_ops;
+    if (!ctx->mg.enabled) return graph_substeps(ctx, dt, ops, n_steps, s);
+    // slab mode over NCCL: the substeps carry ncclSend/ncclRecv; issued eagerly on the caller's stream (no host
+    // synchronisation in between), not captured
+    if (!ctx->mg.peer) return substeps_impl(ctx, dt, ops, n_steps, s);
+    // slab mode over peer memory: plain kernels, so they can be replayed -- in graphs of TWO substeps, which leave
+    // the ping-pong state (particle set, block list, sorted-key buffer) where they found it: one capture serves
+    // until the next migration changes the particle count or the row range (mg.cu drops the graphs then)
+    const uint32_t user_flags = ctx->prm.flags;
+    const uint32_t quiet = user_flags & ~MPMK_WRITE_FTRIAL;   // F_trial: last substep of the batch only
+    int left = n_steps, rc = 0;
+    if (!ctx->coherent) {   // first substep after a migration: full radix sort, not worth a graph of its own
+        ctx->prm.flags = left == 1 ? user_flags : quiet;
+        rc = substeps_impl(ctx, dt, ops, 1, s);
+        left -= 1;
+    }
+    while (rc == 0 && left >= 2) {
+        ctx->prm.flags = left == 2 ? user_flags : quiet;
+        rc = graph_substeps(ctx, dt, ops, 2, s);
+        left -= 2;
+    }
+    if (rc == 0 && left == 1) {
+        ctx->prm.flags = user_flags;
+        rc = substeps_impl(ctx, dt, ops, 1, s);
+    }
+    ctx->prm.flags = user_flags;
+    return rc;
 }

@@ -44,6 +44,12 @@ struct MgState {
     int lo0, lo1, hi0, hi1;  // shared plane ranges with rank-1 / rank+1 (empty when lo1 == lo0)
     void* recv_lo;
     void* recv_hi;
+    // peer-memory halo path (mg.cu): this rank's exchange block (flags + double-buffered receive buffers, cudaMalloc'd
+    // and exported over CUDA IPC) and the neighbours' blocks mapped into this process
+    bool peer;
+    unsigned char* my_block;
+    unsigned char* peer_block[2];   // [0] rank-1's block, [1] rank+1's block
+    size_t buf_bytes;               // one receive buffer
 };
 
 struct mpmk_ctx {
@@ -109,6 +115,7 @@ struct mpmk_ctx {
         uint32_t* sorted_keys;
         bool end_coherent;        // ... and the state it leaves behind
         bool end_last_sort_coherent;
+        int64_t kernels;          // kernel launches inside the graph (mpmk_launch_count counts them per replay)
         uint32_t* end_sorted_keys;
         uint32_t* end_keys_alt;
     } graphs[MPMK_GRAPH_CACHE];
@@ -228,6 +235,7 @@ int mpmk_p2g_init(mpmk_ctx* ctx);
 int mpmk_g2p_init(mpmk_ctx* ctx);
 int mpmk_g2p2g_init(mpmk_ctx* ctx);
 int mpmk_launch_g2p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);
+void mpmk_drop_graphs(mpmk_ctx* ctx);
 int mpmk_mg_clear_shared(mpmk_ctx* ctx, cudaStream_t s);
 int mpmk_mg_halo_sum(mpmk_ctx* ctx, cudaStream_t s);
 extern "C" int mpmk_mg_finalize(mpmk_ctx* ctx);

@@ -15,6 +15,7 @@
 // torch.distributed does the rendezvous plumbing (broadcast of the ncclUniqueId), the data path is
 // this file's ncclSend/ncclRecv over NVLink.
 #include <dlfcn.h>
+#include <stdlib.h>
 #include <nccl.h>
 
 #include "common.cuh"
@@ -93,6 +94,9 @@ extern "C" int mpmk_mg_finalize(mpmk_ctx* ctx) {
     if (!ctx) return 0;
     if (ctx->mg.comm && g_nccl.handle) g_nccl.CommDestroy((ncclComm_t)ctx->mg.comm);
     ctx->mg.comm = nullptr;
+    for (int k = 0; k < 2; ++k) if (ctx->mg.peer_block[k]) { cudaIpcCloseMemHandle(ctx->mg.peer_block[k]); ctx->mg.peer_block[k] = nullptr; }
+    if (ctx->mg.my_block) { cudaFree(ctx->mg.my_block); ctx->mg.my_block = nullptr; }
+    ctx->mg.peer = false;
     ctx->mg.enabled = false;
     return 0;
 }
@@ -115,6 +119,7 @@ extern "C" int mpmk_mg_set_slab(mpmk_ctx* ctx, int x_lo, int x_hi, int ghost, in
         MPMK_FAIL(ctx, MPMK_ERR_INVALID, "mpmk_mg_set_slab: receive buffers missing");
     m.recv_lo = recv_lo_dev; m.recv_hi = recv_hi_dev;
     m.enabled = m.world > 1;
+    mpmk_drop_graphs(ctx);   // captured substeps hold the old plane / row ranges
     return 0;
 }
 
@@ -127,6 +132,7 @@ extern "C" int mpmk_mg_set_count(mpmk_ctx* ctx, int64_t n) {
     ctx->coherent = false;
     ctx->sorted_valid = false;
     ctx->prepared = false;
+    mpmk_drop_graphs(ctx);
     return 0;
 }
 
@@ -168,11 +174,160 @@ int mpmk_mg_clear_shared(mpmk_ctx* ctx, cudaStream_t s) {
     return 0;
 }
 
+
+// ---- peer-memory halo path ---------------------------------------------------------------------------------
+// Instead of ncclSend/ncclRecv, every rank PUSHES its partial sums of the shared planes straight into a receive
+// buffer in the neighbour's memory (stores over NVLink through a CUDA-IPC mapping), then raises a flag there with a
+// system-scope release; the neighbour's add kernel spins on its own flag (acquire) and adds the buffer.  No
+// collective, no rendezvous kernel, nothing on the host: a substep costs one small copy kernel per neighbour and
+// one add kernel.  Exchange block layout (bytes): [0,256) control words, then buf[side][parity], side 0 = data coming
+// from rank-1, side 1 = from rank+1, parity = substep epoch & 1.  Two buffers per side are enough: a sender can only
+// be two pushes ahead of the receiver's add if it has already consumed the receiver's push of the substep in
+// between, which the receiver issues after that add (stream order).
+#define MGP_FLAG_LO 0    // epoch of the last complete push from rank-1 (written by rank-1)
+#define MGP_FLAG_HI 1    // ... from rank+1
+#define MGP_EPOCH 2      // substeps exchanged so far (local)
+#define MGP_DONE_LO 3    // block-done counters of the two push kernels and the add kernel (local)
+#define MGP_DONE_HI 4
+#define MGP_DONE_ADD 5
+#define MGP_CTRL_BYTES 256
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// copy my partial sums of planes [x0, x0+nx) x rows [y0, y0+ny) into the neighbour's buffer of this epoch's parity,
+// then publish epoch+1 in the neighbour's flag
+__global__ void __launch_bounds__(256) k_halo_push(const float4* __restrict__ gin, float4* __restrict__ peer_buf, size_t buf_f4,
+                                                   uint32_t* peer_flag, uint32_t* my_ctrl, int done_word, int x0, int nx, int y0,
+                                                   int ny, int n) {
+    const uint32_t e = my_ctrl[MGP_EPOCH];
+    float4* dst = peer_buf + (size_t)(e & 1u) * buf_f4;
+    const int64_t per_plane = (int64_t)ny * n, total = per_plane * nx;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t px = i / per_plane, rem = i - px * per_plane;
+        dst[i] = gin[((int64_t)(x0 + px) * n + y0) * n + rem];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0 && atomicAdd(&my_ctrl[done_word], 1u) == gridDim.x - 1) {
+        my_ctrl[done_word] = 0u;
+        __threadfence_system();
+        st_release_sys(peer_flag, e + 1u);
+    }
+}
+
+// wait for both neighbours' pushes of this epoch, add them (a + b here, b + a there: bit-identical sums), advance the epoch
+__global__ void __launch_bounds__(256) k_halo_wait_add(float4* __restrict__ gin, const float4* __restrict__ buf_lo,
+                                                       const float4* __restrict__ buf_hi, size_t buf_f4, uint32_t* my_ctrl,
+                                                       int lo0, int nlo, int hi0, int nhi, int y0, int ny, int n) {
+    const uint32_t e = my_ctrl[MGP_EPOCH];
+    if (threadIdx.x == 0) {
+        if (nlo > 0) while (ld_acquire_sys(&my_ctrl[MGP_FLAG_LO]) < e + 1u) {}
+        if (nhi > 0) while (ld_acquire_sys(&my_ctrl[MGP_FLAG_HI]) < e + 1u) {}
+    }
+    __syncthreads();
+    const int64_t per_plane = (int64_t)ny * n;
+    const int64_t tlo = per_plane * nlo, total = tlo + per_plane * nhi;
+    const float4* blo = buf_lo + (size_t)(e & 1u) * buf_f4;
+    const float4* bhi = buf_hi + (size_t)(e & 1u) * buf_f4;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const bool hi = i >= tlo;
+        const int64_t j = hi ? i - tlo : i;
+        const int64_t px = j / per_plane, rem = j - px * per_plane;
+        float4* g = gin + (((int64_t)((hi ? hi0 : lo0) + px) * n + y0) * n + rem);
+        const float4 b = __ldcg((hi ? bhi : blo) + j);   // written by the peer: never through this SM's L1
+        float4 a = *g;
+        a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+        *g = a;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && atomicAdd(&my_ctrl[MGP_DONE_ADD], 1u) == gridDim.x - 1) {
+        my_ctrl[MGP_DONE_ADD] = 0u;
+        my_ctrl[MGP_EPOCH] = e + 1u;   // read by the next substep's kernels (later launches on the stream)
+    }
+}
+
+static int halo_sum_peer(mpmk_ctx* ctx, cudaStream_t s) {
+    const MgState& m = ctx->mg;
+    const int n = ctx->n_grid, ny = m.y_hi - m.y_lo;
+    const size_t buf_f4 = m.buf_bytes / 16;
+    if ((size_t)(2 * m.ghost + 2) * ny * n > buf_f4) MPMK_FAIL(ctx, MPMK_ERR_STATE, "peer exchange buffers too small for the shared region");
+    uint32_t* my_ctrl = (uint32_t*)m.my_block;
+    float4* gin = (float4*)ctx->b.grid_in;
+    // my data for rank-1 lands in ITS side-1 buffers (I am its rank+1) and raises its FLAG_HI; for rank+1: side 0, FLAG_LO
+    if (m.lo1 > m.lo0) {
+        float4* pb = (float4*)(m.peer_block[0] + MGP_CTRL_BYTES + 2 * m.buf_bytes);
+        k_halo_push<<<ctx->sm_count * 2, 256, 0, s>>>(gin, pb, buf_f4, (uint32_t*)m.peer_block[0] + MGP_FLAG_HI, my_ctrl, MGP_DONE_LO,
+                                                     m.lo0, m.lo1 - m.lo0, m.y_lo, ny, n);
+        MPMK_LAUNCH_CHECK(ctx);
+    }
+    if (m.hi1 > m.hi0) {
+        float4* pb = (float4*)(m.peer_block[1] + MGP_CTRL_BYTES);
+        k_halo_push<<<ctx->sm_count * 2, 256, 0, s>>>(gin, pb, buf_f4, (uint32_t*)m.peer_block[1] + MGP_FLAG_LO, my_ctrl, MGP_DONE_HI,
+                                                     m.hi0, m.hi1 - m.hi0, m.y_lo, ny, n);
+        MPMK_LAUNCH_CHECK(ctx);
+    }
+    const float4* my_lo = (const float4*)(m.my_block + MGP_CTRL_BYTES);
+    const float4* my_hi = (const float4*)(m.my_block + MGP_CTRL_BYTES + 2 * m.buf_bytes);
+    k_halo_wait_add<<<ctx->sm_count * 2, 256, 0, s>>>(gin, my_lo, my_hi, buf_f4, my_ctrl, m.lo0, m.lo1 - m.lo0, m.hi0, m.hi1 - m.hi0,
+                                                     m.y_lo, ny, n);
+    MPMK_LAUNCH_CHECK(ctx);
+    return 0;
+}
+
+// allocate this rank's exchange block and export it; handle_out receives the 64-byte cudaIpcMemHandle_t
+extern "C" int mpmk_mg_peer_alloc(mpmk_ctx* ctx, int64_t buf_bytes, void* handle_out, int handle_bytes) {
+    if (!ctx || !handle_out || handle_bytes < (int)sizeof(cudaIpcMemHandle_t) || buf_bytes <= 0 || (buf_bytes & 15)) return MPMK_ERR_INVALID;
+    MgState& m = ctx->mg;
+    if (m.my_block) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_mg_peer_alloc: already allocated");
+    MPMK_CHECK(ctx, cudaSetDevice(ctx->device));
+    const size_t total = MGP_CTRL_BYTES + 4 * (size_t)buf_bytes;
+    MPMK_CHECK(ctx, cudaMalloc((void**)&m.my_block, total));
+    MPMK_CHECK(ctx, cudaMemset(m.my_block, 0, total));
+    MPMK_CHECK(ctx, cudaDeviceSynchronize());
+    cudaIpcMemHandle_t h;
+    MPMK_CHECK(ctx, cudaIpcGetMemHandle(&h, m.my_block));
+    memcpy(handle_out, &h, sizeof(h));
+    m.buf_bytes = (size_t)buf_bytes;
+    return 0;
+}
+
+// map the neighbours' exchange blocks (handles from their mpmk_mg_peer_alloc; NULL at the outer ranks) and switch
+// the halo sum of mpmk_substep(s) to the peer-memory path
+extern "C" int mpmk_mg_peer_open(mpmk_ctx* ctx, const void* handle_lo, const void* handle_hi) {
+    if (!ctx) return MPMK_ERR_INVALID;
+    MgState& m = ctx->mg;
+    if (!m.my_block) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_mg_peer_open: call mpmk_mg_peer_alloc first");
+    MPMK_CHECK(ctx, cudaSetDevice(ctx->device));
+    const void* hs[2] = {handle_lo, handle_hi};
+    for (int k = 0; k < 2; ++k) {
+        if (!hs[k]) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, hs[k], sizeof(h));
+        void* p = nullptr;
+        MPMK_CHECK(ctx, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        m.peer_block[k] = (unsigned char*)p;
+    }
+    m.peer = true;
+    return 0;
+}
+
+extern "C" int mpmk_mg_peer_enabled(mpmk_ctx* ctx) { return ctx && ctx->mg.peer ? 1 : 0; }
+
 // symmetric halo sum of the shared region with both neighbours: one send + one receive per plane
 // (rows [y_lo, y_hi) of a plane are one contiguous run of (y_hi - y_lo) * n float4), all in one group
 int mpmk_mg_halo_sum(mpmk_ctx* ctx, cudaStream_t s) {
     const MgState& m = ctx->mg;
     if (!m.enabled) return 0;
+    static const int skip = getenv("MPMK_MG_SKIP") ? atoi(getenv("MPMK_MG_SKIP")) : 0;   // timing experiments only: wrong physics
+    if (skip >= 2) return 0;
+    if (m.peer) return halo_sum_peer(ctx, s);
     ncclComm_t comm = (ncclComm_t)m.comm;
     const int n = ctx->n_grid, ny = m.y_hi - m.y_lo;
     const size_t run_f = (size_t)ny * n * 4;  // floats per plane run
@@ -180,6 +335,7 @@ int mpmk_mg_halo_sum(mpmk_ctx* ctx, cudaStream_t s) {
     const int r0[2] = {m.lo0, m.hi0}, r1[2] = {m.lo1, m.hi1};
     const int peer[2] = {m.rank - 1, m.rank + 1};
     float* rbuf[2] = {(float*)m.recv_lo, (float*)m.recv_hi};
+    if (skip < 1) {
     NCCL_CHECK(ctx, g_nccl.GroupStart());
     for (int k = 0; k < 2; ++k)
         for (int x = r0[k]; x < r1[k]; ++x) {
@@ -187,6 +343,7 @@ int mpmk_mg_halo_sum(mpmk_ctx* ctx, cudaStream_t s) {
             NCCL_CHECK(ctx, g_nccl.Recv(rbuf[k] + (size_t)(x - r0[k]) * run_f, run_f, ncclFloat32, peer[k], comm, s));
         }
     NCCL_CHECK(ctx, g_nccl.GroupEnd());
+    }
     for (int k = 0; k < 2; ++k) {
         if (r1[k] <= r0[k]) continue;
         k_halo_add<<<ctx->sm_count * 4, 256, 0, s>>>((float4*)gin, (const float4*)rbuf[k], r0[k], r1[k] - r0[k], m.y_lo, ny, n);

@@ -17,6 +17,7 @@ WORKLOADS = {
     "S-4M": (256, 2.0, (88, 88, 88), (80, 80, 80), 1e-4),            # N = 4,096,000
     "S-32M": (512, 2.0, (176, 176, 176), (160, 160, 160), 5e-5),      # N = 32,768,000
     "S-32M-bar": (512, 2.0, (32, 208, 208), (448, 96, 96), 5e-5),     # N = 33,030,144 (multi-GPU slabs)
+    "S-bar1": (512, 2.0, (32, 208, 208), (56, 96, 96), 5e-5),         # N = 4,128,768: one rank's share of S-32M-bar
     "S-512K": (128, 2.0, (44, 44, 44), (40, 40, 40), 2e-4),           # N = 512,000 (tests)
     "S-64K": (64, 2.0, (22, 22, 22), (20, 20, 20), 4e-4),             # N = 64,000 (tests)
 }

@@ -374,6 +374,9 @@ class SlabSimulator:
         z = lambda: torch.zeros((planes * self.n_grid * self.n_grid, 4), dtype=torch.float32, device=self.device)
         self._recv_lo = z() if self.rank > 0 else None
         self._recv_hi = z() if self.rank < self.world - 1 else None
+        self.halo_path = "nccl"
+        if os.environ.get("MPMK_MG_PEER", "1") != "0":
+            self._open_peer_halo(planes)
         self._ops = CudaRecordOps(b, _stream)
         self._auto = migrate_every in (None, 0, "auto")
         self.max_interval = 64
@@ -397,6 +400,24 @@ class SlabSimulator:
         st["ft0"], st["ft1"], st["ft2"] = b.ft   # F_trial of the last substep travels with the particle (export)
         st["keys"] = b.keys
         return st
+
+    def _open_peer_halo(self, planes):
+        """Peer-memory halo path (csrc/mg.cu): every rank exports its exchange block as a CUDA IPC handle, the handles
+        travel once over torch.distributed, the neighbours map them; from then on the per-substep halo sum is stores
+        over NVLink into the neighbour's memory plus a flag -- no NCCL call on the substep path.  One node only."""
+        import ctypes as C
+        b = self.backend
+        hbuf = (C.c_char * 64)()
+        b.ctx.call("mpmk_mg_peer_alloc", planes * self.n_grid * self.n_grid * 16, C.cast(hbuf, C.c_void_p), 64)
+        mine = torch.frombuffer(bytearray(hbuf.raw), dtype=torch.uint8).clone().to(self.device)
+        handles = [torch.empty(64, dtype=torch.uint8, device=self.device) for _ in range(self.world)]
+        dist.all_gather(handles, mine, group=self.group)
+        raw = lambda r: handles[r].cpu().numpy().tobytes()
+        lo = raw(self.rank - 1) if self.rank > 0 else None
+        hi = raw(self.rank + 1) if self.rank < self.world - 1 else None
+        b.ctx.call("mpmk_mg_peer_open", lo, hi)
+        dist.barrier(group=self.group)   # nobody pushes before every mapping exists
+        self.halo_path = "peer"
 
     def _warm_up_p2p(self):
         """one dummy record each way now, so that the first real migration does not pay for setting up the

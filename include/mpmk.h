@@ -231,6 +231,15 @@ MPMK_API int mpmk_mg_unpack(mpmk_ctx* ctx, const void* idx_dev, int64_t first_sl
  * (holes_dev) that lie below n_new; scratch_dev: 8 + 4*n_holes + (n - n_new) bytes                           */
 MPMK_API int mpmk_mg_close_holes(mpmk_ctx* ctx, const void* holes_dev, int64_t n_holes, int64_t n_new, void* scratch_dev,
                                  int64_t scratch_bytes, void* stream);
+/* Peer-memory halo path (same node, NVLink): every rank allocates an exchange block (control words + 4 receive
+ * buffers of buf_bytes: two neighbours x double buffering) and exports it as a 64-byte CUDA IPC handle; the host layer
+ * passes the handles to the neighbours, which map them.  From mpmk_mg_peer_open on, the halo sum of mpmk_substep(s) is
+ * one copy kernel per neighbour that stores this rank's partial sums into the neighbour's memory and raises a flag
+ * there (st.release.sys), and one kernel that waits for the neighbours' flags and adds what they pushed -- no NCCL
+ * call on the substep path.  buf_bytes >= (2*ghost+2) * n_grid^2 * 16 covers any row range.                     */
+MPMK_API int mpmk_mg_peer_alloc(mpmk_ctx* ctx, int64_t buf_bytes, void* handle_out, int handle_bytes);
+MPMK_API int mpmk_mg_peer_open(mpmk_ctx* ctx, const void* handle_lo, const void* handle_hi);
+MPMK_API int mpmk_mg_peer_enabled(mpmk_ctx* ctx);
 /* the halo sum alone (stagewise use: after mpmk_p2g, before mpmk_grid_update)     */
 MPMK_API int mpmk_mg_halo_exchange(mpmk_ctx* ctx, void* stream);
 
