@@ -24,6 +24,10 @@ TOL_X, TOL_F = 1e-4, 1e-4   # max|dx| / grid dx ; relative Frobenius error of co
 
 def run_case(material, S, rank, world, dev, omega, ghost=1, migrate_every=5):
     n_grid, lo, cn, dt = 64, (22, 22, 22), (20, 20, 20), 4e-4
+    if world > 2:   # at least 8 planes per slab (a slab must be >= 2*ghost+2 planes thick)
+        cn = (8 * world, 16, 16)
+        if lo[0] + cn[0] + 4 > n_grid:
+            n_grid, lo, dt = 128, (30, 50, 50), 2e-4
     cloud = synthetic.make_cloud(n_grid, 2.0, lo, cn, seed=5, omega=omega)
     args = synthetic.sim_args(n_grid=n_grid, material=material, substep_dt=dt)
     ops = synthetic.block_ops(n_grid, 2.0, lo, cn)
