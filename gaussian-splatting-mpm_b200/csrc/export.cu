@@ -47,6 +47,56 @@ __global__ void k_export(const float4* __restrict__ xm, const float4* __restrict
     }
 }
 
+// postprocess() + grid2world + the undo chain of render_frame in one pass: position and covariance
+// of every particle in ORIGINAL order, in the frame the rasteriser wants:
+//     p = (x * alpha + beta) M          (main.py:310-313 grid2world, :139-143 undo shift / scale / rotations)
+//     S = M^T (gamma F S0 F^T) M        (utils.py:402-433, main.py:145-146)
+// M = product of the pre-processing rotations in inverse order (transform_utils.py:106-123); alpha, beta, gamma are
+// composed on the host (mpm_solver: utils/transform_utils.py world_affine).
+struct WorldXform {
+    float alpha, gamma;
+    float beta[3];
+    float M[9];
+};
+
+__global__ void k_export_world(const float4* __restrict__ xm, const float4* __restrict__ f0, const float4* __restrict__ f1,
+                               const float4* __restrict__ f2, const int4* __restrict__ meta, const float* __restrict__ init_cov,
+                               float* __restrict__ oxyz, float* __restrict__ ocov, int64_t n, const WorldXform w) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    const int64_t id = meta[r].x;
+    const float4 X = xm[r];
+    const float q[3] = {X.x * w.alpha + w.beta[0], X.y * w.alpha + w.beta[1], X.z * w.alpha + w.beta[2]};
+#pragma unroll
+    for (int c = 0; c < 3; ++c) oxyz[3 * id + c] = q[0] * w.M[c] + q[1] * w.M[3 + c] + q[2] * w.M[6 + c];
+    if (!ocov) return;
+    const float4 F0 = f0[r], F1 = f1[r], F2 = f2[r];
+    const float F[9] = {F0.x, F0.y, F0.z, F0.w, F1.x, F1.y, F1.z, F1.w, F2.x};
+    const float* ic = init_cov + 6 * id;
+    const float c0[9] = {ic[0], ic[1], ic[2], ic[1], ic[3], ic[4], ic[2], ic[4], ic[5]};
+    float t[9], o[9];
+#pragma unroll
+    for (int rr = 0; rr < 3; ++rr)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) t[3 * rr + c] = F[3 * rr] * c0[c] + F[3 * rr + 1] * c0[3 + c] + F[3 * rr + 2] * c0[6 + c];
+#pragma unroll
+    for (int rr = 0; rr < 3; ++rr)
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+            o[3 * rr + c] = (t[3 * rr] * F[3 * c] + t[3 * rr + 1] * F[3 * c + 1] + t[3 * rr + 2] * F[3 * c + 2]) * w.gamma;
+    // M^T o M, upper triangle
+#pragma unroll
+    for (int rr = 0; rr < 3; ++rr)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) t[3 * rr + c] = o[3 * rr] * w.M[c] + o[3 * rr + 1] * w.M[3 + c] + o[3 * rr + 2] * w.M[6 + c];
+    float* oc = ocov + 6 * id;
+    int k = 0;
+#pragma unroll
+    for (int rr = 0; rr < 3; ++rr)
+#pragma unroll
+        for (int c = rr; c < 3; ++c) oc[k++] = w.M[rr] * t[c] + w.M[3 + rr] * t[3 + c] + w.M[6 + rr] * t[6 + c];
+}
+
 __global__ void k_mu_lam(const float* __restrict__ logE, const float* __restrict__ y, float* __restrict__ mu,
                          float* __restrict__ lam, int64_t n) {
     const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -83,6 +133,26 @@ extern "C" int mpmk_export(mpmk_ctx* ctx, const void* init_cov_dev, void* xyz_ou
         (const float4*)A.xm, (const float4*)(ft ? ctx->b.ft0 : A.f0), (const float4*)(ft ? ctx->b.ft1 : A.f1),
         (const float4*)(ft ? ctx->b.ft2 : A.f2), (const int4*)A.meta, (const float*)init_cov_dev, (float*)xyz_out,
         (float*)cov_out, (float*)R_out, ctx->n);
+    MPMK_LAUNCH_CHECK(ctx);
+    return 0;
+}
+
+extern "C" int mpmk_export_world(mpmk_ctx* ctx, const void* init_cov_dev, const mpmk_world_xform* xf, void* xyz_out,
+                                 void* cov_out, void* stream) {
+    if (!ctx || !ctx->bound) return MPMK_ERR_STATE;
+    if (!xf || !xyz_out) MPMK_FAIL(ctx, MPMK_ERR_INVALID, "mpmk_export_world: xf and xyz_out are required");
+    if (ctx->n == 0) return 0;
+    if (cov_out && !init_cov_dev) MPMK_FAIL(ctx, MPMK_ERR_INVALID, "mpmk_export_world: cov_out needs init_cov");
+    const mpmk_particle_set& A = ctx->b.set[ctx->cur];
+    const bool ft = ctx->ftrial_valid;
+    WorldXform w;
+    w.alpha = xf->alpha; w.gamma = xf->gamma;
+    for (int i = 0; i < 3; ++i) w.beta[i] = xf->beta[i];
+    for (int i = 0; i < 9; ++i) w.M[i] = xf->M[i];
+    k_export_world<<<div_up(ctx->n, 128), 128, 0, (cudaStream_t)stream>>>(
+        (const float4*)A.xm, (const float4*)(ft ? ctx->b.ft0 : A.f0), (const float4*)(ft ? ctx->b.ft1 : A.f1),
+        (const float4*)(ft ? ctx->b.ft2 : A.f2), (const int4*)A.meta, (const float*)init_cov_dev, (float*)xyz_out,
+        (float*)cov_out, ctx->n, w);
     MPMK_LAUNCH_CHECK(ctx);
     return 0;
 }

@@ -48,6 +48,10 @@ class SubstepOps(C.Structure):
                 ("impulses", Impulse * MAX_IMPULSES)]
 
 
+class WorldXform(C.Structure):
+    _fields_ = [("alpha", C.c_float), ("gamma", C.c_float), ("beta", C.c_float * 3), ("M", C.c_float * 9)]
+
+
 class Counters(C.Structure):
     _fields_ = [("n_items", C.c_uint32), ("n_active_blocks", C.c_uint32), ("n_tiles", C.c_uint32),
                 ("n_clamped", C.c_uint32)]
@@ -112,6 +116,7 @@ def lib():
         "mpmk_substep": (i, [vp, f, C.POINTER(SubstepOps), vp]),
         "mpmk_substeps": (i, [vp, f, C.POINTER(SubstepOps), i, vp]),
         "mpmk_export": (i, [vp, vp, vp, vp, vp, vp]),
+        "mpmk_export_world": (i, [vp, vp, C.POINTER(WorldXform), vp, vp, vp]),
         "mpmk_read_counters": (i, [vp, C.POINTER(Counters), vp]),
         "mpmk_launch_count": (i64, [vp]),
         "mpmk_mg_init": (i, [vp, C.c_char_p, vp, i, i, i]),

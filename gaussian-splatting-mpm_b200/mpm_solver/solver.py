@@ -243,6 +243,31 @@ class MPM_Simulator:
             self.postprocess()
         return b.out_xyz, b.out_cov, b.out_R
 
+    def export_world(self, scaling_modifier, pos_center, rotation_matrices=(), mode="render", render_scaling_modifier=1.0,
+                     out=None):
+        """Positions [N,3] and covariances [N,6] of the deformed Gaussians, original particle order, in ONE kernel
+        (csrc/export.cu k_export_world) instead of postprocess() + Field.to_torch() + grid2world + the undo chain:
+        mode="grid2world" gives what main.py:310-313 assigns to sim_means3D / sim_covs, mode="render" what
+        render_frame (main.py:139-146) then hands to the rasteriser as means3D / cov3D_precomp."""
+        from utils import transform_utils as T
+        b = self._backend
+        alpha, beta, gamma = T.world_affine(mode, scaling_modifier, pos_center, self.mpm_model.grid_extent, render_scaling_modifier)
+        M = T.inverse_rotation_composite(rotation_matrices) if mode == "render" else [[1, 0, 0], [0, 1, 0], [0, 0, 1]]
+        xf = _native.WorldXform()
+        xf.alpha, xf.gamma = alpha, gamma
+        for k in range(3):
+            xf.beta[k] = float(beta[k])
+            for c in range(3):
+                xf.M[3 * k + c] = float(M[k][c])
+        n = b.out_xyz.shape[0]
+        if out is None:
+            if getattr(b, "world_xyz", None) is None:
+                b.world_xyz = torch.empty((n, 3), dtype=torch.float32, device=b.device)
+                b.world_cov = torch.empty((n, 6), dtype=torch.float32, device=b.device)
+            out = (b.world_xyz, b.world_cov)
+        b.ctx.call("mpmk_export_world", b.init_cov.data_ptr(), C.byref(xf), out[0].data_ptr(), out[1].data_ptr(), _stream())
+        return out
+
     def counters(self):
         c = _native.Counters()
         self._backend.ctx.call("mpmk_read_counters", C.byref(c), _stream())

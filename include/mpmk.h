@@ -193,6 +193,19 @@ MPMK_API int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops,
 MPMK_API int mpmk_export(mpmk_ctx* ctx, const void* init_cov_dev, void* xyz_out_dev /* float[n][3] */,
                 void* cov_out_dev /* float[n][6] */, void* R_out_dev /* float[n][9] */, void* stream);
 
+/* export straight into the rasteriser's frame: postprocess (utils.py:402-433) + grid2world
+ * (utils/transform_utils.py:18-21, main.py:310-313) + render_frame's undo chain (main.py:139-146) in one pass:
+ *   position = (x * alpha + beta) M,   covariance = M^T (gamma * F Sigma0 F^T) M   (upper triangle, 6 floats)
+ * M (row-major) is the product of the pre-processing rotations in inverse order (transform_utils.py:106-123).    */
+typedef struct {
+    float alpha;
+    float gamma;
+    float beta[3];
+    float M[9];
+} mpmk_world_xform;
+MPMK_API int mpmk_export_world(mpmk_ctx* ctx, const void* init_cov_dev, const mpmk_world_xform* xf,
+                               void* xyz_out_dev /* float[n][3] */, void* cov_out_dev /* float[n][6] or NULL */, void* stream);
+
 /* ---- multi-GPU slab decomposition (csrc/mg.cu) ------------------------------
  * The reference is single-GPU (one ti.init(arch=ti.cuda), dense global fields:
  * main.py:28, model.py:118-121); these entry points have no counterpart there.
