@@ -388,9 +388,15 @@ __global__ void __launch_bounds__(CS_THREADS) k_cs_flag_scan(const uint32_t* __r
                                                              uint32_t* __restrict__ samples) {
     __shared__ uint32_t chunk_s, excl_s;
     __shared__ uint32_t wsum[CS_THREADS / 32];
+    __shared__ uint32_t hist_s[OS_MAX_PASSES * 512];
+    // one resident wave of CTAs, each taking 4096-slot chunks by ticket until none are left: a chunk's predecessors
+    // are then mostly finished when it looks back, and there is no second wave waiting for the first to drain
+    for (;;) {
+    __syncthreads();
     if (threadIdx.x == 0) chunk_s = atomicAdd(&ctrl[CS_CTRL_TICKET_A], 1u);
     __syncthreads();
     const uint32_t chunk = chunk_s;
+    if ((int64_t)chunk * CS_CHUNK >= n) return;
     const int w = threadIdx.x >> 5;
     const unsigned lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
@@ -415,7 +421,6 @@ __global__ void __launch_bounds__(CS_THREADS) k_cs_flag_scan(const uint32_t* __r
         if ((int)lane == r) myword = m;
     }
     const uint32_t pc = __popc(myword);
-    __shared__ uint32_t hist_s[OS_MAX_PASSES * 512];
     for (int i = threadIdx.x; i < passes * 512; i += CS_THREADS) hist_s[i] = 0u;
     uint32_t total;
     const uint32_t wordex = cs_chunk_scan(pc, chunk, status, wsum, &excl_s, &total);   // (its barriers also publish hist_s = 0)
@@ -447,6 +452,7 @@ __global__ void __launch_bounds__(CS_THREADS) k_cs_flag_scan(const uint32_t* __r
             if (v) atomicAdd(&ctrl[OS_CTRL_HIST + i], v);
         }
     }
+    }   // next chunk
 }
 
 __global__ void __launch_bounds__(256) k_cs_place_movers(const uint32_t* __restrict__ mk, const uint32_t* __restrict__ mv,
@@ -516,9 +522,12 @@ __global__ void __launch_bounds__(CS_THREADS) k_cs_place_stayers(const uint32_t*
                                                                  uint32_t* __restrict__ out_keys, uint32_t* __restrict__ out_perm) {
     __shared__ uint32_t chunk_s, excl_s;
     __shared__ uint32_t wsum[CS_THREADS / 32];
+    for (;;) {   // persistent over chunks, as k_cs_flag_scan
+    __syncthreads();
     if (threadIdx.x == 0) chunk_s = atomicAdd(&ctrl[CS_CTRL_TICKET_B], 1u);
     __syncthreads();
     const uint32_t chunk = chunk_s;
+    if ((int64_t)chunk * CS_CHUNK >= n) return;
     const int w = threadIdx.x >> 5;
     const unsigned lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
@@ -552,6 +561,7 @@ __global__ void __launch_bounds__(CS_THREADS) k_cs_place_stayers(const uint32_t*
             out_perm[pos] = (uint32_t)slot;
         }
     }
+    }   // next chunk
 }
 
 template <int BITS>
@@ -568,7 +578,7 @@ static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     const uint32_t* okeys = ctx->sorted_keys;
     const uint32_t* keys = (const uint32_t*)ctx->b.keys;
     const int first = passes & 1;   // the compacted movers start in this buffer so that the last radix pass lands in buffer 0
-    k_cs_flag_scan<<<ntiles, CS_THREADS, 0, s>>>(keys, okeys, ctx->n, ctrl, status_a, ctx->cs_mask, ctx->cs_mprefix, ctx->cs_cnt,
+    k_cs_flag_scan<<<min(ntiles, ctx->sm_count * 5), CS_THREADS, 0, s>>>(keys, okeys, ctx->n, ctrl, status_a, ctx->cs_mask, ctx->cs_mprefix, ctx->cs_cnt,
                                                  ctx->cs_mk[first], ctx->cs_mv[first], BITS, passes, ctx->hist_tot);   // hist_tot: 1024 key samples
     MPMK_LAUNCH_CHECK(ctx);
     const uint32_t* m_dev = ctrl + CS_CTRL_MOVERS;
@@ -593,7 +603,7 @@ static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     k_cs_place_movers<<<ctx->sm_count * 4, 256, 0, s>>>(ctx->cs_mk[in], ctx->cs_mv[in], ctrl, okeys, ctx->n, ctx->cs_mask, ctx->cs_mprefix,
                                                         ctx->cs_cnt, mx, ctx->keys_alt, ctx->perm, ctx->hist_tot);
     MPMK_LAUNCH_CHECK(ctx);
-    k_cs_place_stayers<<<ntiles, CS_THREADS, 0, s>>>(keys, ctx->n, ctrl, status_b, ctx->cs_mask, ctx->cs_mprefix, ctx->cs_cnt, mx,
+    k_cs_place_stayers<<<min(ntiles, ctx->sm_count * 4), CS_THREADS, 0, s>>>(keys, ctx->n, ctrl, status_b, ctx->cs_mask, ctx->cs_mprefix, ctx->cs_cnt, mx,
                                                      ctx->keys_alt, ctx->perm);
     MPMK_LAUNCH_CHECK(ctx);
     uint32_t* t = ctx->sorted_keys; ctx->sorted_keys = ctx->keys_alt; ctx->keys_alt = t;
