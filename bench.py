@@ -198,7 +198,7 @@ def run_multi(a, rank, world, local, dev):
     barrier()
     l0 = L.mpmk_launch_count(h)
     sampler = ClockSampler(local) if rank == 0 else None
-    time.sleep(0.3)
+    time.sleep(1.5)   # nvidia-smi is up and polling before the timed region starts (its start-up stalls the GPU for milliseconds)
     t0 = time.time()
     ms = timed(lambda: sl.step(S, dt), a.steps)
     t1 = time.time()
@@ -322,7 +322,7 @@ def main():
     kernels_per_substep = L.mpmk_launch_count(h) - l0
     barrier()
     sampler = ClockSampler(local)
-    time.sleep(0.3)
+    time.sleep(1.5)   # nvidia-smi is up and polling before the timed region starts (its start-up stalls the GPU for milliseconds)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.time()
     ev0.record(stream)
