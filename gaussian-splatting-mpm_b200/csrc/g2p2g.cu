@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(F_WARPS * 32, F_MIN_CTAS) k_g2p2g(const FArgs 
     }
     cp_async_commit();
     int cur_cell = -1;     // cell (0..63) of the run being accumulated, -1 = none
-    float4 acc = zero4;
+    float4 acc = zero4, acc2 = zero4;
 
     while (dA.count > 0) {
         cp_async_wait<0>();
@@ -365,10 +365,10 @@ __global__ void __launch_bounds__(F_WARPS * 32, F_MIN_CTAS) k_g2p2g(const FArgs 
                 if (cur_cell >= 0 && cur_cell < 64 && node_lane) {
                     const int nd = (cur_cell >> 4) * F_TILE_SX + ((cur_cell >> 2) & 3) * 6 + (cur_cell & 3) + noff;
                     float4 t = S.ptile[nd];
-                    t.x += acc.x; t.y += acc.y; t.z += acc.z; t.w += acc.w;
+                    t.x += acc.x + acc2.x; t.y += acc.y + acc2.y; t.z += acc.z + acc2.z; t.w += acc.w;
                     S.ptile[nd] = t;
                 }
-                acc = zero4;
+                acc = zero4; acc2 = zero4;
                 cur_cell = __shfl_sync(0xffffffffu, my_cell, l);
             }
             const unsigned rest = heads & ~((2u << l) - 1u);
@@ -377,10 +377,10 @@ __global__ void __launch_bounds__(F_WARPS * 32, F_MIN_CTAS) k_g2p2g(const FArgs 
             for (; l < end; ++l) {
                 const float4 yw = recY[l];
                 const float4 rw = recR[l];
-                acc.x += rw.w * yw.x + yw.w * rw.x;
-                acc.y += rw.w * yw.y + yw.w * rw.y;
-                acc.z += rw.w * yw.z + yw.w * rw.z;
-                acc.w += yw.w * rw.w;
+                acc.x = fmaf(rw.w, yw.x, acc.x); acc2.x = fmaf(yw.w, rw.x, acc2.x);
+                acc.y = fmaf(rw.w, yw.y, acc.y); acc2.y = fmaf(yw.w, rw.y, acc2.y);
+                acc.z = fmaf(rw.w, yw.z, acc.z); acc2.z = fmaf(yw.w, rw.z, acc2.z);
+                acc.w = fmaf(yw.w, rw.w, acc.w);
             }
         }
         __syncwarp();
@@ -389,7 +389,7 @@ __global__ void __launch_bounds__(F_WARPS * 32, F_MIN_CTAS) k_g2p2g(const FArgs 
             if (cur_cell >= 0 && cur_cell < 64 && node_lane) {
                 const int nd = (cur_cell >> 4) * F_TILE_SX + ((cur_cell >> 2) & 3) * 6 + (cur_cell & 3) + noff;
                 float4 t = S.ptile[nd];
-                t.x += acc.x; t.y += acc.y; t.z += acc.z; t.w += acc.w;
+                t.x += acc.x + acc2.x; t.y += acc.y + acc2.y; t.z += acc.z + acc2.z; t.w += acc.w;
                 S.ptile[nd] = t;
             }
             __syncwarp();
@@ -403,7 +403,7 @@ __global__ void __launch_bounds__(F_WARPS * 32, F_MIN_CTAS) k_g2p2g(const FArgs 
                 }
             }
             cur_cell = -1;
-            acc = zero4;
+            acc = zero4; acc2 = zero4;
         }
         __syncwarp();  // all lanes are done with the tiles, the records and this stage before any is overwritten
         dA = dB; pA = pB;

@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
     }
     cp_async_commit();
     int cur_cell = -1;
-    float4 acc = zero4;
+    float4 acc = zero4, acc2 = zero4;
     int tx = 0, ty = 0, tz = 0;
 
     while (dA.count > 0) {
@@ -204,22 +204,24 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
                     if (cur_cell >= 0 && node_lane) {
                         const int nd = (cur_cell >> 4) * P2G_TILE_SX + ((cur_cell >> 2) & 3) * 6 + (cur_cell & 3) + noff;
                         float4 t = S.tile[nd];
-                        t.x += acc.x; t.y += acc.y; t.z += acc.z; t.w += acc.w;
+                        t.x += acc.x + acc2.x; t.y += acc.y + acc2.y; t.z += acc.z + acc2.z; t.w += acc.w;
                         S.tile[nd] = t;
                     }
-                    acc = zero4;
+                    acc = zero4; acc2 = zero4;
                     cur_cell = __shfl_sync(0xffffffffu, my_cell, l);
                 }
                 const unsigned rest = heads & ~((2u << l) - 1u);  // heads strictly after l
                 const int end = rest ? (__ffs(rest) - 1) : nbatch;
 #pragma unroll 4
                 for (; l < end; ++l) {
+                    // seven FFMAs on two independent accumulator sets (a sum written as rw.w*yw.x + yw.w*rw.x + acc
+                    // compiles to FMUL + FFMA + FADD)
                     const float4 yw = recY[l];
                     const float4 rw = recR[l];
-                    acc.x += rw.w * yw.x + yw.w * rw.x;
-                    acc.y += rw.w * yw.y + yw.w * rw.y;
-                    acc.z += rw.w * yw.z + yw.w * rw.z;
-                    acc.w += yw.w * rw.w;
+                    acc.x = fmaf(rw.w, yw.x, acc.x); acc2.x = fmaf(yw.w, rw.x, acc2.x);
+                    acc.y = fmaf(rw.w, yw.y, acc.y); acc2.y = fmaf(yw.w, rw.y, acc2.y);
+                    acc.z = fmaf(rw.w, yw.z, acc.z); acc2.z = fmaf(yw.w, rw.z, acc2.z);
+                    acc.w = fmaf(yw.w, rw.w, acc.w);
                 }
             }
             __syncwarp();
@@ -228,7 +230,7 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
                 if (cur_cell >= 0 && node_lane) {
                     const int nd = (cur_cell >> 4) * P2G_TILE_SX + ((cur_cell >> 2) & 3) * 6 + (cur_cell & 3) + noff;
                     float4 t = S.tile[nd];
-                    t.x += acc.x; t.y += acc.y; t.z += acc.z; t.w += acc.w;
+                    t.x += acc.x + acc2.x; t.y += acc.y + acc2.y; t.z += acc.z + acc2.z; t.w += acc.w;
                     S.tile[nd] = t;
                 }
                 __syncwarp();
@@ -242,7 +244,7 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
                     }
                 }
                 cur_cell = -1;
-                acc = zero4;
+                acc = zero4; acc2 = zero4;
                 __syncwarp();
             }
             dA = dB; pA = pB; kA = kB;
