@@ -22,6 +22,7 @@
 #endif
 #define MPMK_SORT_CHUNK (MPMK_SORT_CTA * MPMK_SORT_ROUNDS)
 #define MPMK_MAX_RADIX_BITS 9
+#define MPMK_COHERENT_MIN_N 1500000  // particles from which the merge sort (sort.cu) beats the full radix sort
 #define MPMK_GRAPH_CACHE 8          // captured substep batches kept per context
 
 struct DevCounters {

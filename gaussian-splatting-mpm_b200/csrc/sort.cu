@@ -615,7 +615,10 @@ template <int BITS>
 static int sort_all(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     constexpr int D = 1 << BITS;
     const int ntiles = div_up(ctx->n, MPMK_SORT_CHUNK);
-    if (ctx->coherent && !(ctx->prm.flags & MPMK_SORT_FULL)) return sort_coherent<BITS>(ctx, passes, s);
+    // below ~1.5 M particles the full sort's three or four kernels are quicker than the merge's six (measured on the
+    // config-shaped scenes: 240 k particles 37 vs 47 us, 1 M 57 vs 65 us, 3.6 M 87 vs 68 us); MPMK_SORT_MERGE forces it
+    if (ctx->coherent && !(ctx->prm.flags & MPMK_SORT_FULL) && (ctx->n >= MPMK_COHERENT_MIN_N || (ctx->prm.flags & MPMK_SORT_MERGE)))
+        return sort_coherent<BITS>(ctx, passes, s);
     ctx->last_sort_coherent = false;
     const size_t ctrl_words = OS_CTRL_STATUS + (size_t)passes * ntiles * D;
     MPMK_CHECK(ctx, cudaMemsetAsync(ctx->sort_ctrl, 0, ctrl_words * 4, s));

@@ -13,7 +13,7 @@ _ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB_PATH = os.environ.get("MPMK_LIB") or os.path.join(_ROOT, "lib", "libmpmk.so")
 
 MAT_JELLY, MAT_METAL, MAT_SAND, MAT_FOAM, MAT_FLUID, MAT_PLASTICINE = range(6)
-STRICT_Q1, STRICT_Q3, WRITE_FTRIAL, TRACK_COV, SORT_FULL, FUSE_G2P2G = 1, 2, 4, 8, 16, 32
+STRICT_Q1, STRICT_Q3, WRITE_FTRIAL, TRACK_COV, SORT_FULL, FUSE_G2P2G, SORT_MERGE = 1, 2, 4, 8, 16, 32, 64
 OP_FIXED_CUBE, OP_COLLIDER = 0, 1
 MAX_GRID_OPS, MAX_IMPULSES = 16, 8
 

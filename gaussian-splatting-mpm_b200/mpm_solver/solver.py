@@ -66,6 +66,7 @@ class MPM_Simulator:
         self._track_cov = track_cov
         self._sort_full = False
         self._fuse_g2p2g = False
+        self._sort_merge = False
         self._sync_flags()
 
     def load_particles(self, xyzs, covs, volumes):
@@ -100,6 +101,8 @@ class MPM_Simulator:
             f |= _native.SORT_FULL
         if self._fuse_g2p2g:
             f |= _native.FUSE_G2P2G
+        if self._sort_merge:
+            f |= _native.SORT_MERGE
         if self._has_plastic():
             f |= _native.WRITE_FTRIAL  # F_trial != F after a return mapping; export needs F_trial
         self._backend.params.flags = f
@@ -108,7 +111,8 @@ class MPM_Simulator:
     def set_parameters(self, params=None, **kw):
         """Update solver parameters from a dict (not in the reference; north_star asks for it).
         Keys: gravity, E, nu, yield_stress, hardening, xi, plastic_viscosity, softening, friction_angle,
-        strict_q1, strict_q3, track_cov, sort_full (always the full radix sort, never the merge of the movers), fuse_g2p2g (step() runs the gather of one
+        strict_q1, strict_q3, track_cov, sort_full (always the full radix sort, never the merge of the movers), sort_merge (the merge whenever valid,
+        also for small clouds), fuse_g2p2g (step() runs the gather of one
         substep and the scatter of the next as one kernel)."""
         p = dict(params or {})
         p.update(kw)
@@ -128,7 +132,7 @@ class MPM_Simulator:
                 m._logE.fill_(math.log10(v))
             elif k == "nu":
                 m._y.fill_(-math.log(0.49 / v - 1))
-            elif k in ("strict_q1", "strict_q3", "track_cov", "sort_full", "fuse_g2p2g"):
+            elif k in ("strict_q1", "strict_q3", "track_cov", "sort_full", "fuse_g2p2g", "sort_merge"):
                 setattr(self, "_" + k, bool(v))
             else:
                 raise KeyError(k)

@@ -54,6 +54,7 @@ extern "C" {
 #define MPMK_TRACK_COV 8u  /* g2p applies update_cov every substep (utils.py:187-215) */
 #define MPMK_FUSE_G2P2G 32u /* mpmk_substeps: run the g2p of substep i and the p2g of substep i+1 as one kernel
                             * (csrc/g2p2g.cu; halves particle traffic, measured no faster on B200: DESIGN.md 7) */
+#define MPMK_SORT_MERGE 64u /* take the merge path whenever it is valid, also below the size where it pays (tests) */
 #define MPMK_SORT_FULL 16u /* always run the full radix sort (no merge of the few particles that changed cell) */
 
 typedef struct mpmk_ctx mpmk_ctx;

@@ -235,6 +235,7 @@ def test_coherent_sort_bit_exact(cuda_dev, n_grid, lo, cn, ppc, omega, dt, mater
     cloud = synthetic.make_cloud(n_grid, 2.0, lo, cn, ppc=ppc, seed=21, omega=omega)
     args = synthetic.sim_args(n_grid=n_grid, material=material, substep_dt=dt)
     g = make_gpu(cloud, args, cuda_dev)
+    g.set_parameters(sort_merge=True)     # the library only merges from 1.5 M particles on by itself
     n = g.n_particles
     b = g._backend
     seen_coherent, movers = 0, []
@@ -260,6 +261,7 @@ def test_coherent_sort_equals_full_sort_trajectory(cuda_dev):
     ops = synthetic.block_ops(40, 2.0, (12, 12, 12), (8, 8, 8))
     a = make_gpu(cloud, args, cuda_dev, ops)
     b = make_gpu(cloud, args, cuda_dev, ops)
+    a.set_parameters(sort_merge=True)
     b.set_parameters(sort_full=True)
     a.step(30, 1e-4); b.step(30, 1e-4)
     assert _sort_info(a)[0] == 1 and _sort_info(b)[0] == 0
@@ -375,6 +377,13 @@ def test_full_size_properties(cuda_dev):
     assert torch.isfinite(x).all() and torch.isfinite(cov).all()
     RtR = torch.einsum("nji,njk->nik", R, R)
     assert (RtR - torch.eye(3, device=cuda_dev)).abs().max().item() < 1e-4     # R in O(3)
+    # the sort after a g2p takes the merge path at this size: bit-exact against numpy at the full 4.1 M keys
+    keys = b.keys[:n].cpu().numpy().view(np.uint32).copy()
+    sk, pm = _sorted_state(g)
+    coh, movers = _sort_info(g)
+    assert coh == 1 and 0 < movers < n // 4
+    ref = np.argsort(keys, kind="stable").astype(np.uint32)
+    assert np.array_equal(pm, ref) and np.array_equal(sk, keys[ref])
 
 
 @pytest.mark.gpu
