@@ -320,6 +320,20 @@ extern "C" int mpmk_mg_peer_open(mpmk_ctx* ctx, const void* handle_lo, const voi
 
 extern "C" int mpmk_mg_peer_enabled(mpmk_ctx* ctx) { return ctx && ctx->mg.peer ? 1 : 0; }
 
+// back to the NCCL halo path (a neighbour could not map this rank's block, say): unmap, free, forget
+extern "C" int mpmk_mg_peer_close(mpmk_ctx* ctx) {
+    if (!ctx) return MPMK_ERR_INVALID;
+    MgState& m = ctx->mg;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    for (int k = 0; k < 2; ++k) if (m.peer_block[k]) { cudaIpcCloseMemHandle(m.peer_block[k]); m.peer_block[k] = nullptr; }
+    if (m.my_block) { cudaFree(m.my_block); m.my_block = nullptr; }
+    m.peer = false;
+    mpmk_drop_graphs(ctx);
+    cudaGetLastError();
+    return 0;
+}
+
 // symmetric halo sum of the shared region with both neighbours: one send + one receive per plane
 // (rows [y_lo, y_hi) of a plane are one contiguous run of (y_hi - y_lo) * n float4), all in one group
 int mpmk_mg_halo_sum(mpmk_ctx* ctx, cudaStream_t s) {

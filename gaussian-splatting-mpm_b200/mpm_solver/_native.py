@@ -126,6 +126,7 @@ def lib():
         "mpmk_mg_peer_alloc": (i, [vp, i64, vp, i]),
         "mpmk_mg_peer_open": (i, [vp, vp, vp]),
         "mpmk_mg_peer_enabled": (i, [vp]),
+        "mpmk_mg_peer_close": (i, [vp]),
         "mpmk_mg_set_count": (i, [vp, i64]),
         "mpmk_mg_scan": (i, [vp, vp, vp, vp, vp]),
         "mpmk_mg_pack": (i, [vp, vp, i64, vp, vp]),

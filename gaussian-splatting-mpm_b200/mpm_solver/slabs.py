@@ -408,16 +408,30 @@ class SlabSimulator:
         import ctypes as C
         b = self.backend
         hbuf = (C.c_char * 64)()
-        b.ctx.call("mpmk_mg_peer_alloc", planes * self.n_grid * self.n_grid * 16, C.cast(hbuf, C.c_void_p), 64)
+        ok = 1
+        try:
+            b.ctx.call("mpmk_mg_peer_alloc", planes * self.n_grid * self.n_grid * 16, C.cast(hbuf, C.c_void_p), 64)
+        except _native.MpmkError:
+            ok = 0
         mine = torch.frombuffer(bytearray(hbuf.raw), dtype=torch.uint8).clone().to(self.device)
         handles = [torch.empty(64, dtype=torch.uint8, device=self.device) for _ in range(self.world)]
         dist.all_gather(handles, mine, group=self.group)
         raw = lambda r: handles[r].cpu().numpy().tobytes()
         lo = raw(self.rank - 1) if self.rank > 0 else None
         hi = raw(self.rank + 1) if self.rank < self.world - 1 else None
-        b.ctx.call("mpmk_mg_peer_open", lo, hi)
+        if ok:
+            try:
+                b.ctx.call("mpmk_mg_peer_open", lo, hi)
+            except _native.MpmkError:      # no peer access between these two devices
+                ok = 0
+        # every rank or none: the two sides of a halo must use the same path
+        flag = torch.tensor([ok], dtype=torch.int32, device=self.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        if int(flag.item()) == 1:
+            self.halo_path = "peer"
+        else:
+            b.ctx.call("mpmk_mg_peer_close")
         dist.barrier(group=self.group)   # nobody pushes before every mapping exists
-        self.halo_path = "peer"
 
     def _warm_up_p2p(self):
         """one dummy record each way now, so that the first real migration does not pay for setting up the

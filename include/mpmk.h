@@ -254,6 +254,8 @@ MPMK_API int mpmk_mg_close_holes(mpmk_ctx* ctx, const void* holes_dev, int64_t n
 MPMK_API int mpmk_mg_peer_alloc(mpmk_ctx* ctx, int64_t buf_bytes, void* handle_out, int handle_bytes);
 MPMK_API int mpmk_mg_peer_open(mpmk_ctx* ctx, const void* handle_lo, const void* handle_hi);
 MPMK_API int mpmk_mg_peer_enabled(mpmk_ctx* ctx);
+/* unmap / free the exchange blocks and return to the NCCL halo path */
+MPMK_API int mpmk_mg_peer_close(mpmk_ctx* ctx);
 /* the halo sum alone (stagewise use: after mpmk_p2g, before mpmk_grid_update)     */
 MPMK_API int mpmk_mg_halo_exchange(mpmk_ctx* ctx, void* stream);
 
