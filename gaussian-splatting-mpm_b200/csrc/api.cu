@@ -55,6 +55,7 @@ static int create_impl(mpmk_ctx* ctx, int device, int n_grid, double grid_extent
     ALLOC0(ctx, ctx->counters, sizeof(DevCounters));
     ALLOC0(ctx, ctx->dev_stamp, 4);
     MPMK_CHECK(ctx, cudaStreamCreateWithFlags(&ctx->cap_stream, cudaStreamNonBlocking));
+    { int rc = mpmk_sort_init(ctx); if (rc) return rc; }
     { int rc = mpmk_p2g_init(ctx); if (rc) return rc; }
     { int rc = mpmk_g2p_init(ctx); if (rc) return rc; }
     { int rc = mpmk_g2p2g_init(ctx); if (rc) return rc; }

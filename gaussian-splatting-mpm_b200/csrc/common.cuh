@@ -232,11 +232,11 @@ int mpmk_item_size(const mpmk_ctx* ctx);
 int mpmk_launch_p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);
 int mpmk_launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);
 int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s);
+int mpmk_sort_init(mpmk_ctx* ctx);
 int mpmk_p2g_init(mpmk_ctx* ctx);
 int mpmk_g2p_init(mpmk_ctx* ctx);
 int mpmk_g2p2g_init(mpmk_ctx* ctx);
 int mpmk_launch_g2p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);
 void mpmk_drop_graphs(mpmk_ctx* ctx);
-int mpmk_mg_clear_shared(mpmk_ctx* ctx, cudaStream_t s);
 int mpmk_mg_halo_sum(mpmk_ctx* ctx, cudaStream_t s);
 extern "C" int mpmk_mg_finalize(mpmk_ctx* ctx);

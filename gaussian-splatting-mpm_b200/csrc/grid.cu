@@ -77,7 +77,9 @@ __global__ void __launch_bounds__(256) k_grid_planes(float4* __restrict__ gin, f
         const int ix = x0 + (int)(i / per_plane);
         const int64_t rem = i % per_plane;
         const int iy = y0 + (int)(rem / n), iz = (int)(rem % n);
-        grid_node_update(gin, gout, ix, iy, iz, n, dx, dt, gx, gy, gz, ops, 0);
+        // zeroes grid_in behind itself: the shared planes collect sums from the neighbours on nodes no local block list
+        // knows about, so they are reset here, densely, instead of by a separate clear before the next scatter
+        grid_node_update(gin, gout, ix, iy, iz, n, dx, dt, gx, gy, gz, ops, 1);
     }
 }
 

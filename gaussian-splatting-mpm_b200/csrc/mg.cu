@@ -8,8 +8,8 @@
 // n^2 float4 slices of grid_in: no packing) with ncclSend/ncclRecv in one group on the caller's
 // stream, and each adds what it received: a + b on one side, b + a on the other, bit-identical.  Both
 // then run the (deterministic, per-node) grid update on the shared planes themselves, so no
-// velocities travel back.  The shared planes are cleared and updated densely; everything else stays
-// on the sparse block lists.
+// velocities travel back.  The shared planes are updated densely (and reset behind the update, grid.cu
+// k_grid_planes); everything else stays on the sparse block lists.
 //
 // NCCL is reached through dlopen of the library torch already loaded (path passed by the host layer):
 // torch.distributed does the rendezvous plumbing (broadcast of the ncclUniqueId), the data path is
@@ -149,31 +149,6 @@ __global__ void k_halo_add(float4* __restrict__ gin, const float4* __restrict__ 
         *g = a;
     }
 }
-
-__global__ void k_region_clear(float4* __restrict__ gin, float4* __restrict__ gout, int x0, int nx, int y0, int ny, int n) {
-    const int64_t per_plane = (int64_t)ny * n, total = per_plane * nx;
-    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t px = i / per_plane, rem = i - px * per_plane;
-        const int64_t node = ((int64_t)(x0 + px) * n + y0) * n + rem;
-        gin[node] = z;
-        gout[node] = z;
-    }
-}
-
-// model.py:124-127 on the shared region (dense; the block lists do not know what neighbours add there)
-int mpmk_mg_clear_shared(mpmk_ctx* ctx, cudaStream_t s) {
-    const MgState& m = ctx->mg;
-    const int r0[2] = {m.lo0, m.hi0}, r1[2] = {m.lo1, m.hi1};
-    for (int k = 0; k < 2; ++k) {
-        if (r1[k] <= r0[k]) continue;
-        k_region_clear<<<ctx->sm_count * 4, 256, 0, s>>>((float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out, r0[k], r1[k] - r0[k],
-                                                         m.y_lo, m.y_hi - m.y_lo, ctx->n_grid);
-        MPMK_LAUNCH_CHECK(ctx);
-    }
-    return 0;
-}
-
 
 // ---- peer-memory halo path ---------------------------------------------------------------------------------
 // Instead of ncclSend/ncclRecv, every rank PUSHES its partial sums of the shared planes straight into a receive

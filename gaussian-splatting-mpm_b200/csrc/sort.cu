@@ -583,11 +583,6 @@ static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     MPMK_LAUNCH_CHECK(ctx);
     const uint32_t* m_dev = ctrl + CS_CTRL_MOVERS;
     constexpr int stage_bytes = 2 * MPMK_SORT_CHUNK * 4 + (1024 / 32) * D * 4;   // staging + per-warp digit counters
-    static bool attr_set = false;
-    if (!attr_set) {
-        MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 1024, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, stage_bytes));
-        attr_set = true;
-    }
     int in = first;
     const int mgrid = ntiles < ctx->sm_count ? ntiles : ctx->sm_count;   // persistent: CTAs loop over the movers' tiles
     for (int p = 0; p < passes; ++p) {
@@ -630,11 +625,6 @@ static int sort_all(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     const uint32_t* kin = (const uint32_t*)ctx->b.keys;
     const uint32_t* vin = nullptr;
     constexpr int stage_bytes = 2 * MPMK_SORT_CHUNK * 4 + (256 / 32) * D * 4;
-    static bool attr_set = false;  // more than 48 KB of shared memory: opt in once
-    if (!attr_set) {
-        MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 256, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, stage_bytes));
-        attr_set = true;
-    }
     for (int p = 0; p < passes; ++p) {
         const int o = (passes - 1 - p) & 1;
         k_sort_onesweep<BITS, 256, 16><<<ntiles, 256, stage_bytes, s>>>(kin, vin, kb[o], vb[o], ctx->n, nullptr, p * BITS, ctx->sort_ctrl + OS_CTRL_HIST + p * 512,
@@ -644,6 +634,25 @@ static int sort_all(mpmk_ctx* ctx, int passes, cudaStream_t s) {
         kin = kb[o];
         vin = vb[o];
     }
+    return 0;
+}
+
+// more than 48 KB of shared memory per CTA: opt in, per context (= per device), for every digit width
+template <int BITS>
+static int sort_init_bits(mpmk_ctx* ctx) {
+    constexpr int D = 1 << BITS;
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 256, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         2 * MPMK_SORT_CHUNK * 4 + (256 / 32) * D * 4));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 1024, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         2 * MPMK_SORT_CHUNK * 4 + (1024 / 32) * D * 4));
+    return 0;
+}
+
+int mpmk_sort_init(mpmk_ctx* ctx) {
+    int rc;
+    if ((rc = sort_init_bits<5>(ctx)) || (rc = sort_init_bits<6>(ctx)) || (rc = sort_init_bits<7>(ctx)) ||
+        (rc = sort_init_bits<8>(ctx)) || (rc = sort_init_bits<9>(ctx)))
+        return rc;
     return 0;
 }
 

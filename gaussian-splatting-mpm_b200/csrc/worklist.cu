@@ -114,7 +114,7 @@ int mpmk_launch_prepare(mpmk_ctx* ctx, cudaStream_t s) {
                                                      ctx->block_list[prev], ctx->block_count[prev], ctx->n_grid, ctx->nb,
                                                      ctx->dev_stamp, ctx->counters, ctx->block_count[next], ctx->keep_grid_in ? 0 : 1);
     MPMK_LAUNCH_CHECK(ctx);
-    if (ctx->mg.enabled) { int rc = mpmk_mg_clear_shared(ctx, s); if (rc) return rc; }
+    // (slab mode: the shared planes are reset by k_grid_planes, which visits every node of them each substep)
     if (ctx->n > 0) {
         k_tile_runs<<<min(div_up(ctx->n, 1024), ctx->sm_count * 8), 256, 0, s>>>(ctx->sorted_keys, ctx->n, ctx->tile_list, ctx->tile_end, ctx->counters);
         MPMK_LAUNCH_CHECK(ctx);
