@@ -90,6 +90,59 @@ __global__ void __launch_bounds__(256) k_sort_digit_hist(const uint32_t* __restr
     }
 }
 
+// inclusive scan of two values across the CTA: shuffles inside the warps, one hop through shared memory for the warp
+// totals (three barriers; the log-step shared-memory scan this replaces cost two per step)
+template <int CTA>
+__device__ __forceinline__ void os_block_scan2(uint32_t& a, uint32_t& b, uint32_t& tot_a, uint32_t& tot_b, uint32_t* wsum) {
+    constexpr int NW = CTA / 32;
+    const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t ta = __shfl_up_sync(0xffffffffu, a, o), tb = __shfl_up_sync(0xffffffffu, b, o);
+        if (lane >= (unsigned)o) { a += ta; b += tb; }
+    }
+    if (lane == 31) { wsum[w] = a; wsum[32 + w] = b; }
+    __syncthreads();
+    if (w == 0) {
+        uint32_t va = lane < NW ? wsum[lane] : 0u, vb = lane < NW ? wsum[32 + lane] : 0u;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t ta = __shfl_up_sync(0xffffffffu, va, o), tb = __shfl_up_sync(0xffffffffu, vb, o);
+            if (lane >= (unsigned)o) { va += ta; vb += tb; }
+        }
+        wsum[lane] = va; wsum[32 + lane] = vb;
+    }
+    __syncthreads();
+    if (w > 0) { a += wsum[w - 1]; b += wsum[32 + w - 1]; }
+    tot_a = wsum[NW - 1]; tot_b = wsum[32 + NW - 1];
+    __syncthreads();   // wsum is free again
+}
+
+// one batch of the look-back: B status words per unfinished digit, all loads issued before any is looked at
+template <int D, int CTA, int DPT, int B>
+__device__ __forceinline__ void os_lookback(const uint32_t* status, uint32_t (&excl)[DPT], int64_t (&tb)[DPT], bool (&done)[DPT]) {
+    uint32_t v[DPT][B];
+#pragma unroll
+    for (int q = 0; q < DPT; ++q) {
+        const int d = threadIdx.x + q * CTA;
+#pragma unroll
+        for (int b = 0; b < B; ++b)
+            v[q][b] = (!done[q] && tb[q] - b >= 0) ? *((volatile const uint32_t*)&status[(size_t)(tb[q] - b) * D + d]) : OS_FLAG_INC;
+    }
+#pragma unroll
+    for (int q = 0; q < DPT; ++q) {
+        if (done[q]) continue;
+        int b = 0;
+#pragma unroll
+        for (; b < B; ++b) {
+            if ((v[q][b] & (OS_FLAG_AGG | OS_FLAG_INC)) == 0u) break;   // that tile is still counting: reload from it
+            excl[q] += v[q][b] & OS_MASK;
+            if (v[q][b] & OS_FLAG_INC) { done[q] = true; break; }
+        }
+        tb[q] -= b;
+    }
+}
+
 // CTA threads rank ROUNDS keys each: 256 x 16 for the full sort; 1024 x 4 for the coherent sort's few movers, where
 // the latency of one tile, not throughput, is what a pass costs (same tile size, hence the same status layout)
 template <int BITS, int CTA, int ROUNDS>
@@ -111,8 +164,7 @@ __global__ void __launch_bounds__(CTA) k_sort_onesweep(const uint32_t* __restric
     uint32_t* skey = os_stage;
     uint32_t* sval = os_stage + CHUNK;
     uint32_t (*wh)[D] = reinterpret_cast<uint32_t (*)[D]>(os_stage + 2 * CHUNK);   // per-warp digit counters
-    __shared__ uint32_t part[CTA];
-    __shared__ uint32_t parth[CTA];   // the global digit histogram rides along in the same scans -> exclusive digit bases
+    __shared__ uint32_t wsum[64];     // warp totals of the two block scans
     __shared__ uint32_t tile_s;
     uint32_t hcount[DPT], hbase[DPT];
 #pragma unroll
@@ -187,74 +239,46 @@ __global__ void __launch_bounds__(CTA) k_sort_onesweep(const uint32_t* __restric
             atomicExch(&status[(size_t)tile * D + d], run | (tile == 0 ? OS_FLAG_INC : OS_FLAG_AGG));
         }
     }
-    // tile-local exclusive scan over the digits
+    // tile-local exclusive scan over the digits (thread t holds digits t and t+CTA: two sweeps when DPT == 2); the
+    // global digit histogram rides along in the same scans -> exclusive digit bases
     {
-        uint32_t s = 0;
-#pragma unroll
-        for (int q = 0; q < DPT; ++q) s += total[q];
-        // thread t holds digits t and t+CTA: scan in digit order needs two sweeps when DPT == 2
-        part[threadIdx.x] = total[0];
-        parth[threadIdx.x] = hcount[0];
-        __syncthreads();
-        for (int o = 1; o < CTA; o <<= 1) {
-            const uint32_t v = (threadIdx.x >= o) ? part[threadIdx.x - o] : 0u;
-            const uint32_t vh = (threadIdx.x >= o) ? parth[threadIdx.x - o] : 0u;
-            __syncthreads();
-            part[threadIdx.x] += v;
-            parth[threadIdx.x] += vh;
-            __syncthreads();
-        }
-        const uint32_t lo_total = part[CTA - 1];  // count of digits [0, CTA)
-        const uint32_t lo_htotal = parth[CTA - 1];
-        if (threadIdx.x < D) lstart[threadIdx.x] = part[threadIdx.x] - total[0];
-        hbase[0] = parth[threadIdx.x] - hcount[0];
-        __syncthreads();
+        uint32_t ia = total[0], ih = hcount[0], lo_total, lo_htotal;
+        os_block_scan2<CTA>(ia, ih, lo_total, lo_htotal, wsum);
+        if (threadIdx.x < D) lstart[threadIdx.x] = ia - total[0];
+        hbase[0] = ih - hcount[0];
         if (DPT == 2) {
-            part[threadIdx.x] = total[DPT - 1];
-            parth[threadIdx.x] = hcount[DPT - 1];
-            __syncthreads();
-            for (int o = 1; o < CTA; o <<= 1) {
-                const uint32_t v = (threadIdx.x >= o) ? part[threadIdx.x - o] : 0u;
-                const uint32_t vh = (threadIdx.x >= o) ? parth[threadIdx.x - o] : 0u;
-                __syncthreads();
-                part[threadIdx.x] += v;
-                parth[threadIdx.x] += vh;
-                __syncthreads();
-            }
-            if (threadIdx.x + CTA < D) lstart[threadIdx.x + CTA] = lo_total + part[threadIdx.x] - total[DPT - 1];
-            hbase[DPT - 1] = lo_htotal + parth[threadIdx.x] - hcount[DPT - 1];
-            __syncthreads();
+            uint32_t hi_total, hi_htotal;
+            ia = total[DPT - 1]; ih = hcount[DPT - 1];
+            os_block_scan2<CTA>(ia, ih, hi_total, hi_htotal, wsum);
+            if (threadIdx.x + CTA < D) lstart[threadIdx.x + CTA] = lo_total + ia - total[DPT - 1];
+            hbase[DPT - 1] = lo_htotal + ih - hcount[DPT - 1];
         }
-        (void)s;
     }
-    // decoupled look-back: count of digit d in all earlier tiles
+    // decoupled look-back: count of digit d in all earlier tiles.  The first batch reads the eight tiles behind us
+    // (independent loads); when none of them has its inclusive count yet -- all tiles started together, the
+    // coherent sort's few mover tiles or a small scene -- the walk goes on 32 tiles at a time, and a thread's two
+    // digits walk side by side, so the chain is a couple of L2 round trips instead of one per eight tiles per digit
+    {
+        uint32_t excl[DPT];
+        int64_t tb[DPT];
+        bool done[DPT];
 #pragma unroll
-    for (int q = 0; q < DPT; ++q) {
-        const int d = threadIdx.x + q * CTA;
-        if (d < D) {
-            uint32_t excl = 0;
-            if (tile > 0) {
-                // walk back over the earlier tiles eight status words at a time (independent loads): with all tiles
-                // resident at once -- the coherent sort's few tiles -- a one-by-one walk is a chain of L2 round trips
-                int64_t t = (int64_t)tile - 1;
-                bool done = false;
-                while (!done) {
-                    uint32_t v[8];
+        for (int q = 0; q < DPT; ++q) { excl[q] = 0u; tb[q] = (int64_t)tile - 1; done[q] = (threadIdx.x + q * CTA >= D) || tile == 0; }
+        os_lookback<D, CTA, DPT, 8>(status, excl, tb, done);
+        for (;;) {
+            bool all = true;
 #pragma unroll
-                    for (int b = 0; b < 8; ++b)
-                        v[b] = (t - b >= 0) ? *((volatile const uint32_t*)&status[(size_t)(t - b) * D + d]) : OS_FLAG_INC;
-                    int b = 0;
+            for (int q = 0; q < DPT; ++q) all = all && done[q];
+            if (all) break;
+            os_lookback<D, CTA, DPT, 32>(status, excl, tb, done);
+        }
 #pragma unroll
-                    for (; b < 8; ++b) {
-                        if ((v[b] & (OS_FLAG_AGG | OS_FLAG_INC)) == 0u) break;   // that tile is still counting: reload from it
-                        excl += v[b] & OS_MASK;
-                        if (v[b] & OS_FLAG_INC) { done = true; break; }
-                    }
-                    t -= b;
-                }
-                atomicExch(&status[(size_t)tile * D + d], (excl + total[q]) | OS_FLAG_INC);
+        for (int q = 0; q < DPT; ++q) {
+            const int d = threadIdx.x + q * CTA;
+            if (d < D) {
+                if (tile > 0) atomicExch(&status[(size_t)tile * D + d], (excl[q] + total[q]) | OS_FLAG_INC);
+                gdelta[d] = hbase[q] + excl[q] - lstart[d];
             }
-            gdelta[d] = hbase[q] + excl - lstart[d];
         }
     }
     __syncthreads();
@@ -582,12 +606,12 @@ static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s) {
                                                  ctx->cs_mk[first], ctx->cs_mv[first], BITS, passes, ctx->hist_tot);   // hist_tot: 1024 key samples
     MPMK_LAUNCH_CHECK(ctx);
     const uint32_t* m_dev = ctrl + CS_CTRL_MOVERS;
-    constexpr int stage_bytes = 2 * MPMK_SORT_CHUNK * 4 + (1024 / 32) * D * 4;   // staging + per-warp digit counters
+    constexpr int stage_bytes = 2 * MPMK_SORT_CHUNK * 4 + (512 / 32) * D * 4;   // staging + per-warp digit counters
     int in = first;
     const int mgrid = ntiles < ctx->sm_count ? ntiles : ctx->sm_count;   // persistent: CTAs loop over the movers' tiles
     for (int p = 0; p < passes; ++p) {
         const int o = 1 - in;
-        k_sort_onesweep<BITS, 1024, 4><<<mgrid, 1024, stage_bytes, s>>>(ctx->cs_mk[in], ctx->cs_mv[in], ctx->cs_mk[o], ctx->cs_mv[o], 0, m_dev,
+        k_sort_onesweep<BITS, 512, 8><<<mgrid, 512, stage_bytes, s>>>(ctx->cs_mk[in], ctx->cs_mv[in], ctx->cs_mk[o], ctx->cs_mv[o], 0, m_dev,
                                                                p * BITS, ctx->sort_ctrl + OS_CTRL_HIST + p * 512,
                                                                ctrl + OS_CTRL_STATUS + (size_t)p * ntiles * D, ctrl + p);
         MPMK_LAUNCH_CHECK(ctx);
@@ -615,7 +639,12 @@ static int sort_all(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     if (ctx->coherent && !(ctx->prm.flags & MPMK_SORT_FULL) && (ctx->n >= MPMK_COHERENT_MIN_N || (ctx->prm.flags & MPMK_SORT_MERGE)))
         return sort_coherent<BITS>(ctx, passes, s);
     ctx->last_sort_coherent = false;
-    const size_t ctrl_words = OS_CTRL_STATUS + (size_t)passes * ntiles * D;
+    // small clouds re-sort in full every substep, and there a pass costs the latency of ONE tile (a warp's serial
+    // instruction stream: ranking rounds, re-staging, write-out), not throughput: twice the threads, half the rounds
+    // (quarter-size tiles were tried: the look-back chain over four times the tiles costs more than they save)
+    const bool small = ctx->n < MPMK_COHERENT_MIN_N;
+    const int otiles = ntiles;
+    const size_t ctrl_words = OS_CTRL_STATUS + (size_t)passes * otiles * D;
     MPMK_CHECK(ctx, cudaMemsetAsync(ctx->sort_ctrl, 0, ctrl_words * 4, s));
     int hgrid = ntiles < ctx->sm_count * 4 ? ntiles : ctx->sm_count * 4;
     k_sort_digit_hist<BITS><<<hgrid, 256, 0, s>>>((const uint32_t*)ctx->b.keys, ctx->n, nullptr, passes, ctx->sort_ctrl);
@@ -625,11 +654,17 @@ static int sort_all(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     const uint32_t* kin = (const uint32_t*)ctx->b.keys;
     const uint32_t* vin = nullptr;
     constexpr int stage_bytes = 2 * MPMK_SORT_CHUNK * 4 + (256 / 32) * D * 4;
+    constexpr int stage_bytes_small = 2 * MPMK_SORT_CHUNK * 4 + (512 / 32) * D * 4;
     for (int p = 0; p < passes; ++p) {
         const int o = (passes - 1 - p) & 1;
-        k_sort_onesweep<BITS, 256, 16><<<ntiles, 256, stage_bytes, s>>>(kin, vin, kb[o], vb[o], ctx->n, nullptr, p * BITS, ctx->sort_ctrl + OS_CTRL_HIST + p * 512,
-                                                               ctx->sort_ctrl + OS_CTRL_STATUS + (size_t)p * ntiles * D,
-                                                               ctx->sort_ctrl + p);
+        uint32_t* hist = ctx->sort_ctrl + OS_CTRL_HIST + p * 512;
+        uint32_t* status = ctx->sort_ctrl + OS_CTRL_STATUS + (size_t)p * otiles * D;
+        if (small)
+            k_sort_onesweep<BITS, 512, 8><<<otiles, 512, stage_bytes_small, s>>>(
+                kin, vin, kb[o], vb[o], ctx->n, nullptr, p * BITS, hist, status, ctx->sort_ctrl + p);
+        else
+            k_sort_onesweep<BITS, 256, 16><<<otiles, 256, stage_bytes, s>>>(kin, vin, kb[o], vb[o], ctx->n, nullptr, p * BITS, hist, status,
+                                                                            ctx->sort_ctrl + p);
         MPMK_LAUNCH_CHECK(ctx);
         kin = kb[o];
         vin = vb[o];
@@ -643,6 +678,8 @@ static int sort_init_bits(mpmk_ctx* ctx) {
     constexpr int D = 1 << BITS;
     MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 256, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          2 * MPMK_SORT_CHUNK * 4 + (256 / 32) * D * 4));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 512, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         2 * MPMK_SORT_CHUNK * 4 + (512 / 32) * D * 4));
     MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 1024, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          2 * MPMK_SORT_CHUNK * 4 + (1024 / 32) * D * 4));
     return 0;

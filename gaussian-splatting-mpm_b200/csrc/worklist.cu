@@ -63,30 +63,47 @@ __global__ void __launch_bounds__(256) k_tile_runs(const uint32_t* __restrict__ 
 }
 
 // pass 2 over the non-empty tiles: work items (chunks of <= MPMK_ITEM_MAX particles) and the node blocks
-// the tile's stencils reach
+// the tile's stencils reach.  G lanes share a tile: the reference-sized grids (50^3 .. 100^3 cells) have a few
+// hundred tiles holding thousands of particles each, and one thread writing a tile's dozens of items was the
+// longest of the small kernels there; the big sparse grids keep one thread per tile.
+template <int G>
 __global__ void __launch_bounds__(256) k_build_items(const uint2* __restrict__ tile_list, const uint32_t* __restrict__ tile_end,
                                                      uint4* __restrict__ items, DevCounters* cnt, uint32_t* __restrict__ stamp_arr,
                                                      const uint32_t* __restrict__ stamp_ptr, uint32_t* __restrict__ blist,
                                                      uint32_t* __restrict__ bcount, int nt, int nb, uint32_t item_max) {
     const uint32_t n_tiles = cnt->n_tiles;
     const uint32_t stamp = *stamp_ptr;
-    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n_tiles; t += gridDim.x * blockDim.x) {
-        const uint2 tl = tile_list[t];
+    const uint32_t gl = threadIdx.x % G;   // lane within the tile's group
+    const uint32_t groups = gridDim.x * (256 / G);
+    // whole warps stay in the loop together (the shuffle below needs every lane)
+    for (uint32_t t0 = blockIdx.x * (256 / G) + (threadIdx.x & ~31u) / G; t0 < n_tiles; t0 += groups) {
+        const uint32_t t = t0 + (threadIdx.x & 31u) / G;
+        const bool live = t < n_tiles;
+        uint2 tl = make_uint2(0u, 0u);
+        uint32_t np = 0, ni = 0, base = 0;
+        if (live) {
+            tl = tile_list[t];
+            np = tile_end[tl.x] - tl.y;
+            ni = (np + item_max - 1) / item_max;
+            if (gl == 0) base = atomicAdd(&cnt->n_items, ni);
+        }
+        if (G > 1) base = __shfl_sync(0xffffffffu, base, 0, G);
         const uint32_t tile = tl.x, r = tl.y;
-        const uint32_t np = tile_end[tile] - r;
-        const uint32_t ni = (np + item_max - 1) / item_max;
-        const uint32_t base = atomicAdd(&cnt->n_items, ni);
-        for (uint32_t j = 0; j < ni; ++j) {
+        for (uint32_t j = gl; j < ni; j += G) {
             const uint32_t b0 = j * item_max;
             items[base + j] = make_uint4(r + b0, min(item_max, np - b0), tile, 0u);
         }
-        const int tz = tile % nt, ty = (tile / nt) % nt, tx = tile / (nt * nt);
+        if (live) {
+            const int tz = tile % nt, ty = (tile / nt) % nt, tx = tile / (nt * nt);
 #pragma unroll
-        for (int d = 0; d < 8; ++d) {
-            const int bx = tx + (d >> 2), by = ty + ((d >> 1) & 1), bz = tz + (d & 1);
-            if (bx < nb && by < nb && bz < nb) {
-                const uint32_t b = (uint32_t)((bx * nb + by) * nb + bz);
-                if (atomicExch(&stamp_arr[b], stamp) != stamp) blist[atomicAdd(bcount, 1u)] = b;
+            for (int d0 = 0; d0 < 8; d0 += G) {
+                const int d = d0 + (int)(gl & 7u);
+                if (G > 8 && gl >= 8) break;
+                const int bx = tx + (d >> 2), by = ty + ((d >> 1) & 1), bz = tz + (d & 1);
+                if (bx < nb && by < nb && bz < nb) {
+                    const uint32_t b = (uint32_t)((bx * nb + by) * nb + bz);
+                    if (atomicExch(&stamp_arr[b], stamp) != stamp) blist[atomicAdd(bcount, 1u)] = b;
+                }
             }
         }
     }
@@ -118,9 +135,17 @@ int mpmk_launch_prepare(mpmk_ctx* ctx, cudaStream_t s) {
     if (ctx->n > 0) {
         k_tile_runs<<<min(div_up(ctx->n, 1024), ctx->sm_count * 8), 256, 0, s>>>(ctx->sorted_keys, ctx->n, ctx->tile_list, ctx->tile_end, ctx->counters);
         MPMK_LAUNCH_CHECK(ctx);
-        k_build_items<<<ctx->sm_count, 256, 0, s>>>(ctx->tile_list, ctx->tile_end, ctx->items, ctx->counters, ctx->block_stamp,
-                                                    ctx->dev_stamp, ctx->block_list[next], ctx->block_count[next], ctx->nt,
-                                                    ctx->nb, (uint32_t)mpmk_item_size(ctx));
+        // at most nt^3 tiles exist: with few of them a whole warp takes one tile
+        const int64_t tile_bound = min((int64_t)ctx->nt * ctx->nt * ctx->nt, ctx->n);
+        const uint32_t item_max = (uint32_t)mpmk_item_size(ctx);
+        if (tile_bound <= 16384)
+            k_build_items<32><<<(int)min((int64_t)ctx->sm_count * 8, (int64_t)div_up(tile_bound, 8)), 256, 0, s>>>(
+                ctx->tile_list, ctx->tile_end, ctx->items, ctx->counters, ctx->block_stamp, ctx->dev_stamp, ctx->block_list[next],
+                ctx->block_count[next], ctx->nt, ctx->nb, item_max);
+        else
+            k_build_items<1><<<ctx->sm_count, 256, 0, s>>>(ctx->tile_list, ctx->tile_end, ctx->items, ctx->counters, ctx->block_stamp,
+                                                           ctx->dev_stamp, ctx->block_list[next], ctx->block_count[next], ctx->nt,
+                                                           ctx->nb, item_max);
         MPMK_LAUNCH_CHECK(ctx);
     }
     ctx->cur_list = next;
