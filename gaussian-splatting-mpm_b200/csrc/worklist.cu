@@ -35,29 +35,49 @@ __global__ void k_clear_blocks(float4* __restrict__ gin, float4* __restrict__ go
 // list, the last one records the run's end in the tile-indexed table (no search, no dependent loads)
 __global__ void __launch_bounds__(256) k_tile_runs(const uint32_t* __restrict__ skeys, int64_t n, uint2* __restrict__ tile_list,
                                                    uint32_t* __restrict__ tile_end, DevCounters* cnt) {
-    // four consecutive keys per thread (one 16-byte load); the neighbours' edge keys come through shuffles, only the
-    // warp's two outer lanes touch memory again
+    // sixteen consecutive keys per thread (four 16-byte loads in flight); the neighbours' edge keys come through
+    // shuffles, only the warp's two outer lanes touch memory again; one list append per warp
+    constexpr int K = 16;
     const unsigned lane = threadIdx.x & 31;
-    for (int64_t r0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; r0 - 4 * (int64_t)lane < n; r0 += (int64_t)gridDim.x * blockDim.x * 4) {
-        uint32_t t[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-        if (r0 + 4 <= n) {
-            const uint4 v = *reinterpret_cast<const uint4*>(skeys + r0);
-            t[0] = v.x >> 6; t[1] = v.y >> 6; t[2] = v.z >> 6; t[3] = v.w >> 6;
+    for (int64_t r0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * K; r0 - K * (int64_t)lane < n; r0 += (int64_t)gridDim.x * blockDim.x * K) {
+        uint32_t t[K];
+        if (r0 + K <= n) {
+            const uint4* p = reinterpret_cast<const uint4*>(skeys + r0);
+            uint4 v[K / 4];
+#pragma unroll
+            for (int q = 0; q < K / 4; ++q) v[q] = p[q];
+#pragma unroll
+            for (int q = 0; q < K / 4; ++q) { t[4 * q] = v[q].x >> 6; t[4 * q + 1] = v[q].y >> 6; t[4 * q + 2] = v[q].z >> 6; t[4 * q + 3] = v[q].w >> 6; }
         } else {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) if (r0 + q < n) t[q] = skeys[r0 + q] >> 6;
+            for (int q = 0; q < K; ++q) t[q] = (r0 + q < n) ? (skeys[r0 + q] >> 6) : 0xffffffffu;
         }
-        uint32_t prev = __shfl_up_sync(0xffffffffu, t[3], 1);
+        uint32_t prev = __shfl_up_sync(0xffffffffu, t[K - 1], 1);
         uint32_t next = __shfl_down_sync(0xffffffffu, t[0], 1);
         if (lane == 0) prev = (r0 > 0 && r0 - 1 < n) ? (skeys[r0 - 1] >> 6) : 0xffffffffu;
-        if (lane == 31) next = (r0 + 4 < n) ? (skeys[r0 + 4] >> 6) : 0xffffffffu;
+        if (lane == 31) next = (r0 + K < n) ? (skeys[r0 + K] >> 6) : 0xffffffffu;
+        uint32_t starts = 0u;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            if (r0 + q >= n) break;
-            const uint32_t p = q ? t[q - 1] : prev;
-            const uint32_t nx = q < 3 ? t[q + 1] : next;
-            if (t[q] != p) tile_list[atomicAdd(&cnt->n_tiles, 1u)] = make_uint2(t[q], (uint32_t)(r0 + q));
-            if (t[q] != nx) tile_end[t[q]] = (uint32_t)(r0 + q) + 1u;
+        for (int q = 0; q < K; ++q) {
+            if (r0 + q < n) {
+                const uint32_t p = q ? t[q - 1] : prev;
+                const uint32_t nx = q < K - 1 ? t[q + 1] : next;
+                if (t[q] != p) starts |= 1u << q;
+                if (t[q] != nx) tile_end[t[q]] = (uint32_t)(r0 + q) + 1u;
+            }
+        }
+        const uint32_t c = __popc(starts);
+        uint32_t incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= (unsigned)o) incl += u; }
+        const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+        if (total) {
+            uint32_t base = 0u;
+            if (lane == 31) base = atomicAdd(&cnt->n_tiles, total);
+            uint32_t at = __shfl_sync(0xffffffffu, base, 31) + incl - c;
+#pragma unroll
+            for (int q = 0; q < K; ++q)
+                if (starts & (1u << q)) tile_list[at++] = make_uint2(t[q], (uint32_t)(r0 + q));
         }
     }
 }
@@ -85,25 +105,45 @@ __global__ void __launch_bounds__(256) k_build_items(const uint2* __restrict__ t
             tl = tile_list[t];
             np = tile_end[tl.x] - tl.y;
             ni = (np + item_max - 1) / item_max;
-            if (gl == 0) base = atomicAdd(&cnt->n_items, ni);
         }
-        if (G > 1) base = __shfl_sync(0xffffffffu, base, 0, G);
+        if (G == 1) {   // one append per warp
+            const unsigned lane = threadIdx.x & 31u;
+            uint32_t incl = ni;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= (unsigned)o) incl += u; }
+            if (lane == 31u) base = atomicAdd(&cnt->n_items, incl);
+            base = __shfl_sync(0xffffffffu, base, 31) + incl - ni;
+        } else {
+            if (live && gl == 0) base = atomicAdd(&cnt->n_items, ni);
+            base = __shfl_sync(0xffffffffu, base, 0, G);
+        }
         const uint32_t tile = tl.x, r = tl.y;
         for (uint32_t j = gl; j < ni; j += G) {
             const uint32_t b0 = j * item_max;
             items[base + j] = make_uint4(r + b0, min(item_max, np - b0), tile, 0u);
         }
-        if (live) {
-            const int tz = tile % nt, ty = (tile / nt) % nt, tx = tile / (nt * nt);
+        const int tz = tile % nt, ty = (tile / nt) % nt, tx = tile / (nt * nt);
 #pragma unroll
-            for (int d0 = 0; d0 < 8; d0 += G) {
-                const int d = d0 + (int)(gl & 7u);
-                if (G > 8 && gl >= 8) break;
+        for (int d0 = 0; d0 < 8; d0 += G) {
+            const int d = d0 + (int)(gl & 7u);
+            bool fresh = false;
+            uint32_t b = 0u;
+            if (live && (G <= 8 || gl < 8)) {
                 const int bx = tx + (d >> 2), by = ty + ((d >> 1) & 1), bz = tz + (d & 1);
                 if (bx < nb && by < nb && bz < nb) {
-                    const uint32_t b = (uint32_t)((bx * nb + by) * nb + bz);
-                    if (atomicExch(&stamp_arr[b], stamp) != stamp) blist[atomicAdd(bcount, 1u)] = b;
+                    b = (uint32_t)((bx * nb + by) * nb + bz);
+                    fresh = atomicExch(&stamp_arr[b], stamp) != stamp;
                 }
+            }
+            // newly stamped blocks: one list append per warp
+            const unsigned m = __ballot_sync(0xffffffffu, fresh);
+            if (m) {
+                const unsigned lane = threadIdx.x & 31u;
+                const int leader = __ffs(m) - 1;
+                uint32_t bbase = 0u;
+                if ((int)lane == leader) bbase = atomicAdd(bcount, (uint32_t)__popc(m));
+                bbase = __shfl_sync(0xffffffffu, bbase, leader);
+                if (fresh) blist[bbase + __popc(m & ((1u << lane) - 1u))] = b;
             }
         }
     }
@@ -133,7 +173,7 @@ int mpmk_launch_prepare(mpmk_ctx* ctx, cudaStream_t s) {
     MPMK_LAUNCH_CHECK(ctx);
     // (slab mode: the shared planes are reset by k_grid_planes, which visits every node of them each substep)
     if (ctx->n > 0) {
-        k_tile_runs<<<min(div_up(ctx->n, 1024), ctx->sm_count * 8), 256, 0, s>>>(ctx->sorted_keys, ctx->n, ctx->tile_list, ctx->tile_end, ctx->counters);
+        k_tile_runs<<<min(div_up(ctx->n, 4096), ctx->sm_count * 8), 256, 0, s>>>(ctx->sorted_keys, ctx->n, ctx->tile_list, ctx->tile_end, ctx->counters);
         MPMK_LAUNCH_CHECK(ctx);
         // at most nt^3 tiles exist: with few of them a whole warp takes one tile
         const int64_t tile_bound = min((int64_t)ctx->nt * ctx->nt * ctx->nt, ctx->n);
