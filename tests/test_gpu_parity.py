@@ -267,8 +267,8 @@ def test_coherent_sort_equals_full_sort_trajectory(cuda_dev):
     assert _sort_info(a)[0] == 1 and _sort_info(b)[0] == 0
     assert np.array_equal(a._backend.ids().cpu().numpy(), b._backend.ids().cpu().numpy())   # same particle in every slot
     xa, ca, _ = a.export(); xb, cb, _ = b.export()
-    assert (xa - xb).abs().max().item() <= 2.4e-7
-    assert rel_fro(ca.cpu().numpy(), cb.cpu().numpy()) < 1e-5
+    assert (xa - xb).abs().max().item() <= 1e-6   # a few ulp of x ~ 1 (observed: <= 2 ulp; the atomics' order varies run to run)
+    assert rel_fro(ca.cpu().numpy(), cb.cpu().numpy()) < 5e-5
 
 
 @pytest.mark.parametrize("material,omega,dt", [
@@ -300,17 +300,20 @@ def test_fused_g2p2g_equals_unfused(cuda_dev, material, omega, dt):
     assert np.array_equal(a._backend.ids().cpu().numpy(), b._backend.ids().cpu().numpy())
     xa, ca, _ = a.export(); xb, cb, _ = b.export()
     dx = 2.0 / n_grid
-    assert (xa - xb).abs().max().item() < 3e-5 * dx      # a few ulp of x ~ 1 (dx = 1/32)
-    assert rel_fro(ca.cpu().numpy(), cb.cpu().numpy()) < 1e-5
+    # the two schedules add the same terms in different orders (and the float atomics make each of them vary from run
+    # to run); the plastic return maps amplify that noise over the 20 substeps, so the bounds are SURVEY.md 8c's
+    # stated ones, not a few ulp (observed: 2e-5 * dx, 3e-6, 5e-6; grids 1e-5 .. 5.4e-5)
+    assert (xa - xb).abs().max().item() < 1e-4 * dx
+    assert rel_fro(ca.cpu().numpy(), cb.cpu().numpy()) < 1e-4
     va = a.mpm_state.particle_vel.to_torch().cpu().numpy(); vb = b.mpm_state.particle_vel.to_torch().cpu().numpy()
-    assert rel_fro(va, vb) < 1e-5
+    assert rel_fro(va, vb) < 1e-4
     o.postprocess()
     assert np.abs(xa.cpu().numpy() - o.in_original_order("particle_xyz")).max() < 1e-4 * dx
     assert rel_fro(ca.cpu().numpy().reshape(-1), np.asarray(o.in_original_order("particle_cov")).reshape(-1)) < 1e-4
     # the grid fields hold the last substep's scatter and update, as after a loop of p2g2p() calls
     ga = a._backend.grid_in.cpu().numpy(); gb = b._backend.grid_in.cpu().numpy()
-    assert rel_fro(ga, gb) < 5e-5
-    assert rel_fro(a._backend.grid_out.cpu().numpy(), b._backend.grid_out.cpu().numpy()) < 5e-5
+    assert rel_fro(ga, gb) < 2e-4
+    assert rel_fro(a._backend.grid_out.cpu().numpy(), b._backend.grid_out.cpu().numpy()) < 2e-4
 
 
 def test_substeps_graph_equals_loop(cuda_dev):
@@ -326,8 +329,8 @@ def test_substeps_graph_equals_loop(cuda_dev):
     assert abs(a.time - b.time) < 1e-12
     xa, ca, _ = a.export(); xb, cb, _ = b.export()
     # same kernels, same order of launches; only the float atomics' order may differ
-    assert (xa - xb).abs().max().item() <= 2.4e-7   # 2 ulp of x ~ 1
-    assert rel_fro(ca.cpu().numpy(), cb.cpu().numpy()) < 1e-5
+    assert (xa - xb).abs().max().item() <= 1e-6   # a few ulp of x ~ 1 (observed: <= 2 ulp)
+    assert rel_fro(ca.cpu().numpy(), cb.cpu().numpy()) < 5e-5
 
 
 def test_track_cov_matches_update_cov(cuda_dev):
