@@ -1,6 +1,12 @@
 // api.cu -- C ABI (include/mpmk.h): context lifecycle, the substep driver (solver.py:27-52 order) and
 // CUDA-graph replay of constant-dt substep batches.
 #include "common.cuh"
+#include <cstdlib>
+
+bool mpmk_pdl_enabled() {
+    static const bool on = getenv("MPMK_PDL") && atoi(getenv("MPMK_PDL")) != 0;   // opt-in: see common.cuh
+    return on;
+}
 
 static int ceil_log2(uint64_t v) { int b = 0; while ((1ull << b) < v) ++b; return b; }
 

@@ -150,6 +150,36 @@ struct mpmk_ctx {
 
 static inline int div_up(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
+// ---- programmatic dependent launch (opt-in: MPMK_PDL=1) ------------------------------------------
+// The substep is a chain of a dozen kernels, most of them a few microseconds long; each boundary costs the drain of
+// one grid plus the launch of the next.  With MPMK_PDL=1 the chain's kernels are launched with the
+// programmatic-serialization attribute: the next grid's CTAs become resident while the previous grid's last CTAs
+// are still running and sit in griddepcontrol.wait -- the first statement of every such kernel -- until that grid
+// has completed and its writes are visible.  Every kernel of the chain waits before it touches memory, so
+// completion is transitive along the chain; kernels launched the ordinary way (memsets, the multi-GPU halo kernels,
+// exports) serialise as before.  Measured: it shortens a loop of eager launches (lego-like sort +
+// prepare 52 -> 41 us) but not the graph replay the solver uses (lego-like 0.083 -> 0.082 ms), and costs S-4M
+// 3.6 % there (waiting CTAs of the next grid take residency from the big kernels' tails) -- hence off by default;
+// without the attribute the waits are no-ops.
+__device__ __forceinline__ void pdl_wait() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
+bool mpmk_pdl_enabled();
+
+template <typename... P, typename... A>
+static inline cudaError_t mpmk_launch(void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, A&&... a) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = mpmk_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<P>(a)...);
+}
+
 // ---- device helpers ---------------------------------------------------------------------
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
 

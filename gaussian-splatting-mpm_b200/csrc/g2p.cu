@@ -69,6 +69,7 @@ struct __align__(16) G2PWarpSmem {
 };
 
 __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PArgs a) {
+    pdl_wait();   // programmatic dependent launch: nothing of the previous grid is read or overwritten before this
     extern __shared__ float4 g2p_smem_raw[];
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -336,7 +337,7 @@ int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s) {
         // persistent grid, warps fetch work items dynamically (counters->g2p_cursor, zeroed by prepare)
         int64_t want = (ctx->n / 32 + G2P_WARPS - 1) / G2P_WARPS + 1;
         int64_t cap = (int64_t)ctx->sm_count * ctx->g2p_ctas_per_sm;
-        k_g2p<<<(int)(want < cap ? want : cap), G2P_WARPS * 32, sizeof(G2PWarpSmem) * G2P_WARPS, s>>>(a);
+        mpmk_launch(k_g2p, dim3((int)(want < cap ? want : cap)), dim3(G2P_WARPS * 32), sizeof(G2PWarpSmem) * G2P_WARPS, s, a);
         MPMK_LAUNCH_CHECK(ctx);
     }
     ctx->cur = dst;

@@ -57,6 +57,7 @@ __global__ void __launch_bounds__(256) k_grid(float4* __restrict__ gin, float4* 
                                               const uint32_t* __restrict__ list, const uint32_t* __restrict__ count,
                                               int n, int nb, float dx, float dt, float gx, float gy, float gz,
                                               const GridOpsArg ops, int zero_in) {
+    pdl_wait();   // programmatic dependent launch: nothing of the previous grid is read or overwritten before this
     const int64_t total = (int64_t)(*count) * 64;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         uint32_t b = list[i >> 6];
@@ -92,7 +93,7 @@ int mpmk_launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaS
         a.n_ops = ops->n_ops;
         memcpy(a.ops, ops->ops, sizeof(mpmk_grid_op) * ops->n_ops);
     }
-    k_grid<<<ctx->sm_count * 8, 256, 0, s>>>((float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out,
+    mpmk_launch(k_grid, dim3(ctx->sm_count * 8), dim3(256), 0, s, (float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out,
                                              ctx->block_list[ctx->cur_list], ctx->block_count[ctx->cur_list],
                                              ctx->n_grid, ctx->nb, ctx->dx, dt, ctx->prm.gravity[0], ctx->prm.gravity[1],
                                              ctx->prm.gravity[2], a, ctx->zero_grid_in ? 1 : 0);

@@ -56,6 +56,7 @@ struct P2GArgs {
 };
 
 __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GArgs a) {
+    pdl_wait();   // programmatic dependent launch: nothing of the previous grid is read or overwritten before this
     extern __shared__ float4 smem_raw[];
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -273,7 +274,7 @@ int mpmk_launch_p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaSt
     int64_t want = (ctx->n / 32 + P2G_WARPS - 1) / P2G_WARPS + 1;
     int64_t cap = (int64_t)ctx->sm_count * ctx->p2g_ctas_per_sm;
     int grid = (int)(want < cap ? want : cap);
-    k_p2g<<<grid, P2G_WARPS * 32, smem, s>>>(a);
+    mpmk_launch(k_p2g, dim3(grid), dim3(P2G_WARPS * 32), smem, s, a);
     MPMK_LAUNCH_CHECK(ctx);
     return 0;
 }

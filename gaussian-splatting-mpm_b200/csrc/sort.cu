@@ -47,6 +47,7 @@ int mpmk_launch_keys(mpmk_ctx* ctx, cudaStream_t s) {
 template <int BITS>
 __global__ void __launch_bounds__(256) k_sort_digit_hist(const uint32_t* __restrict__ keys, int64_t n, const uint32_t* n_dev,
                                                          int passes, uint32_t* __restrict__ ctrl) {
+    pdl_wait();   // programmatic dependent launch: nothing of the previous grid is read or overwritten before this
     constexpr int D = 1 << BITS;
     if (n_dev) n = (int64_t)*n_dev;   // coherent sort: the mover count is only known on the device
     __shared__ uint32_t h[OS_MAX_PASSES][D];
@@ -153,6 +154,7 @@ __global__ void __launch_bounds__(CTA) k_sort_onesweep(const uint32_t* __restric
                                                                  const uint32_t* n_dev, int shift,
                                                                  const uint32_t* __restrict__ ghist,
                                                                  uint32_t* __restrict__ status, uint32_t* __restrict__ tile_counter) {
+    pdl_wait();   // programmatic dependent launch: nothing of the previous grid is read or overwritten before this
     constexpr int D = 1 << BITS;
     constexpr int CHUNK = CTA * ROUNDS;
     static_assert(CHUNK == MPMK_SORT_CHUNK, "tile size is part of the control block layout");
@@ -410,6 +412,7 @@ __global__ void __launch_bounds__(CS_THREADS) k_cs_flag_scan(const uint32_t* __r
                                                              uint32_t* __restrict__ cnt, uint32_t* __restrict__ mk,
                                                              uint32_t* __restrict__ mv, int bits, int passes,
                                                              uint32_t* __restrict__ samples) {
+    pdl_wait();   // programmatic dependent launch: nothing of the previous grid is read or overwritten before this
     __shared__ uint32_t chunk_s, excl_s;
     __shared__ uint32_t wsum[CS_THREADS / 32];
     __shared__ uint32_t hist_s[OS_MAX_PASSES * 512];
@@ -485,6 +488,7 @@ __global__ void __launch_bounds__(256) k_cs_place_movers(const uint32_t* __restr
                                                          const uint32_t* __restrict__ mprefix, uint32_t* __restrict__ cnt,
                                                          uint32_t* __restrict__ mx, uint32_t* __restrict__ out_keys,
                                                          uint32_t* __restrict__ out_perm, const uint32_t* __restrict__ samples) {
+    pdl_wait();   // programmatic dependent launch: nothing of the previous grid is read or overwritten before this
     const uint32_t M = ctrl[CS_CTRL_MOVERS];
     const uint32_t N = (uint32_t)n;
     // first level of the searches: 1024 evenly spaced old keys in shared memory
@@ -544,6 +548,7 @@ __global__ void __launch_bounds__(CS_THREADS) k_cs_place_stayers(const uint32_t*
                                                                  const uint32_t* __restrict__ mprefix,
                                                                  const uint32_t* __restrict__ cnt, const uint32_t* __restrict__ mx,
                                                                  uint32_t* __restrict__ out_keys, uint32_t* __restrict__ out_perm) {
+    pdl_wait();   // programmatic dependent launch: nothing of the previous grid is read or overwritten before this
     __shared__ uint32_t chunk_s, excl_s;
     __shared__ uint32_t wsum[CS_THREADS / 32];
     for (;;) {   // persistent over chunks, as k_cs_flag_scan
@@ -602,7 +607,7 @@ static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     const uint32_t* okeys = ctx->sorted_keys;
     const uint32_t* keys = (const uint32_t*)ctx->b.keys;
     const int first = passes & 1;   // the compacted movers start in this buffer so that the last radix pass lands in buffer 0
-    k_cs_flag_scan<<<min(ntiles, ctx->sm_count * 5), CS_THREADS, 0, s>>>(keys, okeys, ctx->n, ctrl, status_a, ctx->cs_mask, ctx->cs_mprefix, ctx->cs_cnt,
+    mpmk_launch(k_cs_flag_scan, dim3(min(ntiles, ctx->sm_count * 5)), dim3(CS_THREADS), 0, s, keys, okeys, ctx->n, ctrl, status_a, ctx->cs_mask, ctx->cs_mprefix, ctx->cs_cnt,
                                                  ctx->cs_mk[first], ctx->cs_mv[first], BITS, passes, ctx->hist_tot);   // hist_tot: 1024 key samples
     MPMK_LAUNCH_CHECK(ctx);
     const uint32_t* m_dev = ctrl + CS_CTRL_MOVERS;
@@ -611,7 +616,7 @@ static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     const int mgrid = ntiles < ctx->sm_count ? ntiles : ctx->sm_count;   // persistent: CTAs loop over the movers' tiles
     for (int p = 0; p < passes; ++p) {
         const int o = 1 - in;
-        k_sort_onesweep<BITS, 512, 8><<<mgrid, 512, stage_bytes, s>>>(ctx->cs_mk[in], ctx->cs_mv[in], ctx->cs_mk[o], ctx->cs_mv[o], 0, m_dev,
+        mpmk_launch(k_sort_onesweep<BITS, 512, 8>, dim3(mgrid), dim3(512), stage_bytes, s, ctx->cs_mk[in], ctx->cs_mv[in], ctx->cs_mk[o], ctx->cs_mv[o], 0, m_dev,
                                                                p * BITS, ctx->sort_ctrl + OS_CTRL_HIST + p * 512,
                                                                ctrl + OS_CTRL_STATUS + (size_t)p * ntiles * D, ctrl + p);
         MPMK_LAUNCH_CHECK(ctx);
@@ -619,10 +624,10 @@ static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     }
     // sorted movers are in buffer `in` (== 0); the other key buffer is free and receives x_t
     uint32_t* mx = ctx->cs_mk[1 - in];
-    k_cs_place_movers<<<ctx->sm_count * 4, 256, 0, s>>>(ctx->cs_mk[in], ctx->cs_mv[in], ctrl, okeys, ctx->n, ctx->cs_mask, ctx->cs_mprefix,
+    mpmk_launch(k_cs_place_movers, dim3(ctx->sm_count * 4), dim3(256), 0, s, ctx->cs_mk[in], ctx->cs_mv[in], ctrl, okeys, ctx->n, ctx->cs_mask, ctx->cs_mprefix,
                                                         ctx->cs_cnt, mx, ctx->keys_alt, ctx->perm, ctx->hist_tot);
     MPMK_LAUNCH_CHECK(ctx);
-    k_cs_place_stayers<<<min(ntiles, ctx->sm_count * 4), CS_THREADS, 0, s>>>(keys, ctx->n, ctrl, status_b, ctx->cs_mask, ctx->cs_mprefix, ctx->cs_cnt, mx,
+    mpmk_launch(k_cs_place_stayers, dim3(min(ntiles, ctx->sm_count * 4)), dim3(CS_THREADS), 0, s, keys, ctx->n, ctrl, status_b, ctx->cs_mask, ctx->cs_mprefix, ctx->cs_cnt, mx,
                                                      ctx->keys_alt, ctx->perm);
     MPMK_LAUNCH_CHECK(ctx);
     uint32_t* t = ctx->sorted_keys; ctx->sorted_keys = ctx->keys_alt; ctx->keys_alt = t;
@@ -647,7 +652,7 @@ static int sort_all(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     const size_t ctrl_words = OS_CTRL_STATUS + (size_t)passes * otiles * D;
     MPMK_CHECK(ctx, cudaMemsetAsync(ctx->sort_ctrl, 0, ctrl_words * 4, s));
     int hgrid = ntiles < ctx->sm_count * 4 ? ntiles : ctx->sm_count * 4;
-    k_sort_digit_hist<BITS><<<hgrid, 256, 0, s>>>((const uint32_t*)ctx->b.keys, ctx->n, nullptr, passes, ctx->sort_ctrl);
+    mpmk_launch(k_sort_digit_hist<BITS>, dim3(hgrid), dim3(256), 0, s, (const uint32_t*)ctx->b.keys, ctx->n, nullptr, passes, ctx->sort_ctrl);
     MPMK_LAUNCH_CHECK(ctx);
     uint32_t* kb[2] = {ctx->sorted_keys, ctx->keys_alt};
     uint32_t* vb[2] = {ctx->perm, ctx->perm_alt};
@@ -660,10 +665,10 @@ static int sort_all(mpmk_ctx* ctx, int passes, cudaStream_t s) {
         uint32_t* hist = ctx->sort_ctrl + OS_CTRL_HIST + p * 512;
         uint32_t* status = ctx->sort_ctrl + OS_CTRL_STATUS + (size_t)p * otiles * D;
         if (small)
-            k_sort_onesweep<BITS, 512, 8><<<otiles, 512, stage_bytes_small, s>>>(
+            mpmk_launch(k_sort_onesweep<BITS, 512, 8>, dim3(otiles), dim3(512), stage_bytes_small, s, 
                 kin, vin, kb[o], vb[o], ctx->n, nullptr, p * BITS, hist, status, ctx->sort_ctrl + p);
         else
-            k_sort_onesweep<BITS, 256, 16><<<otiles, 256, stage_bytes, s>>>(kin, vin, kb[o], vb[o], ctx->n, nullptr, p * BITS, hist, status,
+            mpmk_launch(k_sort_onesweep<BITS, 256, 16>, dim3(otiles), dim3(256), stage_bytes, s, kin, vin, kb[o], vb[o], ctx->n, nullptr, p * BITS, hist, status,
                                                                             ctx->sort_ctrl + p);
         MPMK_LAUNCH_CHECK(ctx);
         kin = kb[o];

@@ -9,6 +9,7 @@
 __global__ void k_clear_blocks(float4* __restrict__ gin, float4* __restrict__ gout, const uint32_t* __restrict__ list,
                                const uint32_t* __restrict__ count, int n, int nb, uint32_t* stamp, DevCounters* cnt,
                                uint32_t* next_count, int clear_in) {
+    pdl_wait();   // programmatic dependent launch: nothing of the previous grid is read or overwritten before this
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         *stamp += 1u;  // consumed by k_build_items (a later launch on the stream)
         // this substep's counters / block list start empty (the previous substep's kernels are done with them)
@@ -35,6 +36,7 @@ __global__ void k_clear_blocks(float4* __restrict__ gin, float4* __restrict__ go
 // list, the last one records the run's end in the tile-indexed table (no search, no dependent loads)
 __global__ void __launch_bounds__(256) k_tile_runs(const uint32_t* __restrict__ skeys, int64_t n, uint2* __restrict__ tile_list,
                                                    uint32_t* __restrict__ tile_end, DevCounters* cnt) {
+    pdl_wait();   // programmatic dependent launch: nothing of the previous grid is read or overwritten before this
     // sixteen consecutive keys per thread (four 16-byte loads in flight); the neighbours' edge keys come through
     // shuffles, only the warp's two outer lanes touch memory again; one list append per warp
     constexpr int K = 16;
@@ -91,6 +93,7 @@ __global__ void __launch_bounds__(256) k_build_items(const uint2* __restrict__ t
                                                      uint4* __restrict__ items, DevCounters* cnt, uint32_t* __restrict__ stamp_arr,
                                                      const uint32_t* __restrict__ stamp_ptr, uint32_t* __restrict__ blist,
                                                      uint32_t* __restrict__ bcount, int nt, int nb, uint32_t item_max) {
+    pdl_wait();   // programmatic dependent launch: nothing of the previous grid is read or overwritten before this
     const uint32_t n_tiles = cnt->n_tiles;
     const uint32_t stamp = *stamp_ptr;
     const uint32_t gl = threadIdx.x % G;   // lane within the tile's group
@@ -167,23 +170,23 @@ int mpmk_launch_prepare(mpmk_ctx* ctx, cudaStream_t s) {
     int prev = ctx->cur_list;
     int next = 1 - prev;
     // clear what the previous substep touched; reset the per-substep counters
-    k_clear_blocks<<<ctx->sm_count * 8, 256, 0, s>>>((float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out,
+    mpmk_launch(k_clear_blocks, dim3(ctx->sm_count * 8), dim3(256), 0, s, (float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out,
                                                      ctx->block_list[prev], ctx->block_count[prev], ctx->n_grid, ctx->nb,
                                                      ctx->dev_stamp, ctx->counters, ctx->block_count[next], ctx->keep_grid_in ? 0 : 1);
     MPMK_LAUNCH_CHECK(ctx);
     // (slab mode: the shared planes are reset by k_grid_planes, which visits every node of them each substep)
     if (ctx->n > 0) {
-        k_tile_runs<<<min(div_up(ctx->n, 4096), ctx->sm_count * 8), 256, 0, s>>>(ctx->sorted_keys, ctx->n, ctx->tile_list, ctx->tile_end, ctx->counters);
+        mpmk_launch(k_tile_runs, dim3(min(div_up(ctx->n, 4096), ctx->sm_count * 8)), dim3(256), 0, s, ctx->sorted_keys, ctx->n, ctx->tile_list, ctx->tile_end, ctx->counters);
         MPMK_LAUNCH_CHECK(ctx);
         // at most nt^3 tiles exist: with few of them a whole warp takes one tile
         const int64_t tile_bound = min((int64_t)ctx->nt * ctx->nt * ctx->nt, ctx->n);
         const uint32_t item_max = (uint32_t)mpmk_item_size(ctx);
         if (tile_bound <= 16384)
-            k_build_items<32><<<(int)min((int64_t)ctx->sm_count * 8, (int64_t)div_up(tile_bound, 8)), 256, 0, s>>>(
+            mpmk_launch(k_build_items<32>, dim3((int)min((int64_t)ctx->sm_count * 8, (int64_t)div_up(tile_bound, 8))), dim3(256), 0, s, 
                 ctx->tile_list, ctx->tile_end, ctx->items, ctx->counters, ctx->block_stamp, ctx->dev_stamp, ctx->block_list[next],
                 ctx->block_count[next], ctx->nt, ctx->nb, item_max);
         else
-            k_build_items<1><<<ctx->sm_count, 256, 0, s>>>(ctx->tile_list, ctx->tile_end, ctx->items, ctx->counters, ctx->block_stamp,
+            mpmk_launch(k_build_items<1>, dim3(ctx->sm_count), dim3(256), 0, s, ctx->tile_list, ctx->tile_end, ctx->items, ctx->counters, ctx->block_stamp,
                                                            ctx->dev_stamp, ctx->block_list[next], ctx->block_count[next], ctx->nt,
                                                            ctx->nb, item_max);
         MPMK_LAUNCH_CHECK(ctx);
