@@ -5,6 +5,7 @@
 //   * the list of node blocks this substep's p2g can touch (consumed by the grid pass and by the
 //     next substep's clear).
 #include "common.cuh"
+#include <cstdlib>
 
 __global__ void k_clear_blocks(float4* __restrict__ gin, float4* __restrict__ gout, const uint32_t* __restrict__ list,
                                const uint32_t* __restrict__ count, int n, int nb, uint32_t* stamp, DevCounters* cnt,
@@ -156,8 +157,10 @@ __global__ void __launch_bounds__(256) k_build_items(const uint2* __restrict__ t
 // (a multiple of the 32-particle batch) so that small scenes -- a few hundred tiles holding hundreds of particles
 // per cell, like the reference's 50^3 configs -- still spread over all SMs.
 int mpmk_item_size(const mpmk_ctx* ctx) {
+    static const int forced = getenv("MPMK_ITEM_SIZE") ? atoi(getenv("MPMK_ITEM_SIZE")) : 0;   // tuning experiments
+    if (forced >= 32 && forced <= MPMK_ITEM_MAX) return forced / 32 * 32;
     const int64_t warps = (int64_t)ctx->sm_count * ctx->g2p_ctas_per_sm * 4;  // resident g2p warps (the larger grid)
-    const int64_t want_items = 4 * warps;
+    const int64_t want_items = 4 * warps;   // (2 x was tried: lego-like -2 %, cupnoodle-like +4 %)
     int64_t sz = MPMK_ITEM_MAX;
     if (ctx->n / MPMK_ITEM_MAX < want_items) sz = ((ctx->n / want_items + 31) / 32) * 32;
     if (sz < MPMK_ITEM_MIN) sz = MPMK_ITEM_MIN;
