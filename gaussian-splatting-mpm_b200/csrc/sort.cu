@@ -144,8 +144,9 @@ __device__ __forceinline__ void os_lookback(const uint32_t* status, uint32_t (&e
     }
 }
 
-// CTA threads rank ROUNDS keys each: 256 x 16 for the full sort; 1024 x 4 for the coherent sort's few movers, where
-// the latency of one tile, not throughput, is what a pass costs (same tile size, hence the same status layout)
+// CTA threads rank ROUNDS keys each: 256 x 16 for the full sort of a large cloud; 512 x 8 for the coherent sort's few
+// movers and for small clouds, where the latency of one tile, not throughput, is what a pass costs (same tile size,
+// hence the same status layout; 1024 x 4 measured slower from ~0.6 M keys on: one CTA per SM)
 template <int BITS, int CTA, int ROUNDS>
 __global__ void __launch_bounds__(CTA) k_sort_onesweep(const uint32_t* __restrict__ keys_in,
                                                                  const uint32_t* __restrict__ vals_in,
@@ -685,8 +686,6 @@ static int sort_init_bits(mpmk_ctx* ctx) {
                                          2 * MPMK_SORT_CHUNK * 4 + (256 / 32) * D * 4));
     MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 512, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          2 * MPMK_SORT_CHUNK * 4 + (512 / 32) * D * 4));
-    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 1024, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         2 * MPMK_SORT_CHUNK * 4 + (1024 / 32) * D * 4));
     return 0;
 }
 
