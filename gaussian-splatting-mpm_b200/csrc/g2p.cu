@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
 #ifdef EXP_NOGATHER
             { const float4 g0 = g[0]; v[0] = g0.x; v[1] = g0.y; v[2] = g0.z; Mx[0] = fx; My[1] = fy; Mz[2] = fz; Gx[0] = wx[0]; Gy[1] = wy[1]; Gz[2] = wz[2] + wzd[0] + dwz[1]; }
 #else
-#pragma unroll
+#pragma unroll 1
             for (int i = 0; i < 3; ++i) {
                 float A[3] = {0, 0, 0}, Ay[3] = {0, 0, 0}, Gyi[3] = {0, 0, 0}, Az[3] = {0, 0, 0}, Gzi[3] = {0, 0, 0};
 #pragma unroll
@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
                     Gzi[0] += wj * dx_; Gzi[1] += wj * dy_; Gzi[2] += wj * dz_;
                 }
                 // contraction along x
-                const float wi = wx[i], wii = wx[i] * ((float)i - fx);
+                const float wi = (i == 0) ? wx[0] : (i == 1) ? wx[1] : wx[2], wii = wi * ((float)i - fx);
                 const float di = (i == 0) ? fx - 1.5f : (i == 1) ? -2.0f * (fx - 1.0f) : fx - 0.5f;
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
