@@ -158,7 +158,7 @@ __global__ void __launch_bounds__(256) k_build_items(const uint2* __restrict__ t
 // per cell, like the reference's 50^3 configs -- still spread over all SMs.
 int mpmk_item_size(const mpmk_ctx* ctx) {
     static const int forced = getenv("MPMK_ITEM_SIZE") ? atoi(getenv("MPMK_ITEM_SIZE")) : 0;   // tuning experiments
-    if (forced >= 32 && forced <= MPMK_ITEM_MAX) return forced / 32 * 32;
+    if (forced >= MPMK_ITEM_MIN && forced <= MPMK_ITEM_MAX) return forced / 32 * 32;   // (the items array is sized for MPMK_ITEM_MIN)
     const int64_t warps = (int64_t)ctx->sm_count * ctx->g2p_ctas_per_sm * 4;  // resident g2p warps (the larger grid)
     const int64_t want_items = 4 * warps;   // (2 x was tried: lego-like -2 %, cupnoodle-like +4 %)
     int64_t sz = MPMK_ITEM_MAX;
