@@ -103,9 +103,13 @@ def run_reference(a, rank, world):
     if rank != 0:
         return
     from harness import synthetic
-    name = a.workload or "S-4M"
+    # N = 1: the S-4M cloud of our arm.  N > 1: our arm runs S-32M-bar/N (every rank a 56 x 96 x 96-cell block of the
+    # bar on the 512^3 grid); the bounded sample of that workload is one rank's share of it, S-bar1
+    multi = max(world, a.gpus) > 1
+    name = a.workload or ("S-bar1" if multi else "S-4M")
     cloud, args, ops = synthetic.workload(name)
     n = cloud["xyz"].shape[0]
+    label = name if not multi else f"S-32M-bar/{max(world, a.gpus)} (sample: one rank's share, {name})"
     times = []
     from oracle import mpm_oracle as O
     cores = len(os.sched_getaffinity(0))
@@ -128,7 +132,7 @@ def run_reference(a, rank, world):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": 1e3 * total / a.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": name, "particles": n, "n_grid": args.n_grid, "material": "jelly (FCR)",
+            "config": {"workload": label, "particles": n, "n_grid": args.n_grid, "material": "jelly (FCR)",
                        "substeps_per_step": sub, "note": "CPU restatement of the reference's Taichi kernels (oracle/mpm_oracle.c, "
                        "OpenMP, omp-atomic P2G); Taichi itself is not installable here"},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": sim.L.orc_num_threads(), "kind": "port", "sample": sample},
