@@ -64,7 +64,6 @@ static int create_impl(mpmk_ctx* ctx, int device, int n_grid, double grid_extent
     { int rc = mpmk_sort_init(ctx); if (rc) return rc; }
     { int rc = mpmk_p2g_init(ctx); if (rc) return rc; }
     { int rc = mpmk_g2p_init(ctx); if (rc) return rc; }
-    { int rc = mpmk_g2p2g_init(ctx); if (rc) return rc; }
     ctx->prm.alpha = 0.0f;
     return 0;
 }
@@ -117,6 +116,11 @@ extern "C" int mpmk_bind(mpmk_ctx* ctx, const mpmk_bindings* b) {
 
 extern "C" int mpmk_set_params(mpmk_ctx* ctx, const mpmk_params* p) {
     if (!ctx || !p) return MPMK_ERR_INVALID;
+    // scalar parameters (gravity, alpha, xi, ...) are passed to the kernels by value, so a captured graph has them
+    // baked in: anything but a pure flags change invalidates the captured batches (flags are part of the cache key)
+    mpmk_params a = ctx->prm, b = *p;
+    a.flags = 0u; b.flags = 0u;
+    if (memcmp(&a, &b, sizeof(a)) != 0) mpmk_drop_graphs(ctx);
     ctx->prm = *p;
     return 0;
 }
@@ -191,27 +195,16 @@ extern "C" int mpmk_substep(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops
     return substep_impl(ctx, dt, ops, (cudaStream_t)stream);
 }
 
-// n >= 1 substeps of constant dt and ops.  With MPMK_FUSE_G2P2G and two or more substeps (single GPU) only the first
-// scatter and the last gather run as stand-alone kernels; in between, the gather of substep i and the scatter of substep i+1 are one kernel
-// (g2p2g.cu).  F_trial is only consumed by export: it is stored by the last g2p of the batch.
+// n >= 1 substeps of constant dt and ops.  F_trial (and the yield stress before the return map) is only consumed by
+// export and by mpmk_constitutive_ex: it is stored by the last g2p of the batch.
 static int substeps_impl(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, int n_steps, cudaStream_t s) {
     const uint32_t user_flags = ctx->prm.flags;
-    const bool fuse = n_steps >= 2 && !ctx->mg.enabled && (user_flags & MPMK_FUSE_G2P2G);
     int rc = 0;
     for (int i = 0; i < n_steps && rc == 0; ++i) {
         const bool last = (i == n_steps - 1);
         ctx->prm.flags = last ? user_flags : (user_flags & ~MPMK_WRITE_FTRIAL);
-        if (!fuse) { rc = substep_impl(ctx, dt, ops, s); continue; }
-        ctx->keep_grid_in = (i > 0);    // the previous fused kernel already scattered this substep into grid_in
-        ctx->zero_grid_in = !last;      // ... and the next one needs grid_in zero where this substep touched it
-        if ((rc = mpmk_launch_sort(ctx, s))) break;
-        if ((rc = mpmk_launch_prepare(ctx, s))) break;
-        if (i == 0 && (rc = mpmk_launch_p2g(ctx, dt, ops, s))) break;
-        if ((rc = mpmk_launch_grid(ctx, dt, ops, s))) break;
-        rc = last ? mpmk_launch_g2p(ctx, dt, s) : mpmk_launch_g2p2g(ctx, dt, ops, s);
+        rc = substep_impl(ctx, dt, ops, s);
     }
-    ctx->keep_grid_in = false;
-    ctx->zero_grid_in = false;
     ctx->prm.flags = user_flags;
     return rc;
 }

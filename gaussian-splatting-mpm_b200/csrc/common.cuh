@@ -64,7 +64,7 @@ struct mpmk_ctx {
     int cur;           // which set holds the current state
     int key_bits;
     int sm_count;
-    int g2p_ctas_per_sm, p2g_ctas_per_sm, g2p2g_ctas_per_sm;  // occupancy-derived persistent grid sizes
+    int g2p_ctas_per_sm, p2g_ctas_per_sm;  // occupancy-derived persistent grid sizes
     // fused batches (g2p2g.cu): the next substep's scatter is already in grid_in when the substep starts, so the
     // clear must leave grid_in alone, and the grid pass zeroes grid_in behind itself for the scatter that follows it
     bool keep_grid_in, zero_grid_in;
@@ -265,8 +265,6 @@ int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s);
 int mpmk_sort_init(mpmk_ctx* ctx);
 int mpmk_p2g_init(mpmk_ctx* ctx);
 int mpmk_g2p_init(mpmk_ctx* ctx);
-int mpmk_g2p2g_init(mpmk_ctx* ctx);
-int mpmk_launch_g2p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);
 void mpmk_drop_graphs(mpmk_ctx* ctx);
 int mpmk_mg_halo_sum(mpmk_ctx* ctx, cudaStream_t s);
 extern "C" int mpmk_mg_finalize(mpmk_ctx* ctx);

@@ -235,7 +235,7 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
             if (a.cp.flags & MPMK_WRITE_FTRIAL) {
                 a.ft0[r] = make_float4(Ft[0], Ft[1], Ft[2], Ft[3]);
                 a.ft1[r] = make_float4(Ft[4], Ft[5], Ft[6], Ft[7]);
-                a.ft2[r] = make_float4(Ft[8], 0.f, 0.f, 0.f);
+                a.ft2[r] = make_float4(Ft[8], F2.w, 0.f, 0.f);   // F2.w: the yield stress before this substep's return map
             }
             if (a.cp.flags & MPMK_TRACK_COV) {
                 // update_cov, utils.py:187-215: cov += dt (grad_v cov + cov grad_v^T)
@@ -278,13 +278,22 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
 
 // utils.py:14-54 on the current set in place (init, and after from_torch edits of F)
 __global__ void k_constitutive(float4* f0, float4* f1, float4* f2, float4* cs, float4* s1, const int4* meta, int64_t n,
-                               float dt, const ConstParams cp) {
+                               float dt, const ConstParams cp, const float4* ft0, const float4* ft1, const float4* ft2,
+                               int use_ys_before) {
     const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n) return;
-    const float4 F0 = f0[r], F1 = f1[r], F2 = f2[r];
+    float4 F0 = f0[r], F1 = f1[r];
+    const float4 F2 = f2[r];
     const int4 m = meta[r];
-    const float Ft[9] = {F0.x, F0.y, F0.z, F0.w, F1.x, F1.y, F1.z, F1.w, F2.x};
-    float mu = F2.y, lam = F2.z, ys = F2.w, Fn[9], s6[6];
+    float F22 = F2.x, ys = F2.w;
+    if (ft0) {   // F_trial as the last g2p stored it (the current F has already been through the return map)
+        F0 = ft0[r]; F1 = ft1[r];
+        const float4 T2 = ft2[r];
+        F22 = T2.x;
+        if (use_ys_before) ys = T2.y;
+    }
+    const float Ft[9] = {F0.x, F0.y, F0.z, F0.w, F1.x, F1.y, F1.z, F1.w, F22};
+    float mu = F2.y, lam = F2.z, Fn[9], s6[6];
     constitutive_update(Ft, m.y, mu, lam, ys, dt, cp, Fn, s6);
     f0[r] = make_float4(Fn[0], Fn[1], Fn[2], Fn[3]);
     f1[r] = make_float4(Fn[4], Fn[5], Fn[6], Fn[7]);
@@ -348,13 +357,17 @@ int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s) {
     return 0;
 }
 
-extern "C" int mpmk_constitutive(mpmk_ctx* ctx, float dt, void* stream) {
+extern "C" int mpmk_constitutive_ex(mpmk_ctx* ctx, float dt, int use_ftrial, int use_ys_before, void* stream) {
     if (!ctx || !ctx->bound) return MPMK_ERR_STATE;
     if (ctx->n == 0) return 0;
+    const bool ft = use_ftrial && ctx->ftrial_valid && ctx->b.ft0 && ctx->b.ft1 && ctx->b.ft2;
     const mpmk_particle_set& A = ctx->b.set[ctx->cur];
-    k_constitutive<<<div_up(ctx->n, 128), 128, 0, (cudaStream_t)stream>>>((float4*)A.f0, (float4*)A.f1, (float4*)A.f2,
-                                                                          (float4*)A.cs, (float4*)A.s1, (const int4*)A.meta,
-                                                                          ctx->n, dt, make_cp(ctx));
+    k_constitutive<<<div_up(ctx->n, 128), 128, 0, (cudaStream_t)stream>>>(
+        (float4*)A.f0, (float4*)A.f1, (float4*)A.f2, (float4*)A.cs, (float4*)A.s1, (const int4*)A.meta, ctx->n, dt, make_cp(ctx),
+        ft ? (const float4*)ctx->b.ft0 : nullptr, ft ? (const float4*)ctx->b.ft1 : nullptr, ft ? (const float4*)ctx->b.ft2 : nullptr,
+        (ft && use_ys_before) ? 1 : 0);
     MPMK_LAUNCH_CHECK(ctx);
     return 0;
 }
+
+extern "C" int mpmk_constitutive(mpmk_ctx* ctx, float dt, void* stream) { return mpmk_constitutive_ex(ctx, dt, 0, 0, stream); }

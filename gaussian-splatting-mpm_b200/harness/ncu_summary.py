@@ -10,7 +10,13 @@ COLS = ["Kernel Name", "Block Size", "Grid Size", "gpu__time_duration.sum", "dra
         "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__issue_active.avg.pct_of_peak_sustained_active",
         "smsp__inst_executed.sum", "l1tex__throughput.avg.pct_of_peak_sustained_active",
         "lts__throughput.avg.pct_of_peak_sustained_elapsed", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
-        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "lts__t_sectors_op_red.sum", "sm__cycles_elapsed.max"]
+        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
+        # atomic / reduction traffic (north_star: "atomic throughput"): L2 sectors of RED and ATOM operations, and the
+        # L1 requests that carried global reductions (k_p2g's tile flush is red.global.add.v4.f32)
+        "lts__t_sectors_op_red.sum", "lts__t_sectors_op_atom.sum", "l1tex__t_set_accesses_pipe_lsu_mem_global_op_red.sum",
+        "l1tex__t_requests_pipe_lsu_mem_global_op_red.sum", "lts__t_sectors_srcunit_tex_op_red.sum",
+        "smsp__inst_executed_op_global_red.sum", "smsp__sass_inst_executed_op_global_red.sum",
+        "sm__cycles_elapsed.max"]
 
 
 def main():

@@ -19,7 +19,6 @@ def main():
     ap.add_argument("--material", default="jelly")
     ap.add_argument("--strict-q1", action="store_true")
     ap.add_argument("--sort-full", action="store_true")
-    ap.add_argument("--fuse", action="store_true")
     ap.add_argument("--warm", type=int, default=30)
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--tag", default=os.environ.get("MPMK_LIB", "default"))
@@ -37,8 +36,8 @@ def main():
         cloud, args, ops = synthetic.workload(a.workload)
         args.material = a.material
     sim = MPM_Simulator(t(cloud["xyz"]), t(cloud["cov"]), t(cloud["vol"]), args, strict_q1=a.strict_q1)
-    if a.sort_full or a.fuse:
-        sim.set_parameters(sort_full=a.sort_full, fuse_g2p2g=a.fuse)
+    if a.sort_full:
+        sim.set_parameters(sort_full=True)
     sim.set_boundary_conditions(ops["boundary_conditions"], args)
     sim.add_surface_collider(ops["collider"]["point"], ops["collider"]["normal"], friction=ops["collider"]["friction"])
     sim.mpm_state.particle_vel.from_torch(t(cloud["vel"]))

@@ -61,6 +61,36 @@ def make_cloud(n_grid, grid_extent, cells_lo, cells_n, ppc=8, seed=SEED, omega=(
     return {"xyz": f(xyz), "vel": f(vel), "cov": f(cov), "vol": f(vol)}
 
 
+BAR = dict(n_grid=512, extent=2.0, lo=(32, 208, 208), block=(56, 96, 96), dt=5e-5)   # S-32M-bar = 8 blocks along x
+
+
+def bar_block(rank, world, seed=SEED):
+    """rank's 56 x 96 x 96-cell block (4,128,768 particles) of the bar that `world` ranks simulate together
+    (bench.py --gpus N, weak scaling); the rigid spin is about the centre of the WHOLE bar"""
+    n_grid, extent, (bx0, by0, bz0), (wx, wy, wz) = BAR["n_grid"], BAR["extent"], BAR["lo"], BAR["block"]
+    dx = extent / n_grid
+    cloud = make_cloud(n_grid, extent, (bx0 + wx * rank, by0, bz0), (wx, wy, wz), seed=seed + rank)
+    centre = np.array([(bx0 + 0.5 * wx * world) * dx, (by0 + 0.5 * wy) * dx, (bz0 + 0.5 * wz) * dx])
+    r = cloud["xyz"].astype(np.float64) - centre
+    cloud["vel"] = np.cross(np.broadcast_to(np.array([0.0, 0.0, 2.0]), r.shape), r).astype(np.float32)
+    return cloud
+
+
+def bar_workload(world, material="jelly"):
+    """(args, ops, bounds) of the bar for `world` ranks"""
+    n_grid, extent, (bx0, by0, bz0), (wx, wy, wz) = BAR["n_grid"], BAR["extent"], BAR["lo"], BAR["block"]
+    args = sim_args(n_grid=n_grid, grid_extent=extent, substep_dt=BAR["dt"], material=material)
+    ops = block_ops(n_grid, extent, (bx0, by0, bz0), (wx * world, wy, wz))
+    bounds = [0] + [bx0 + wx * k for k in range(1, world)] + [n_grid]
+    return args, ops, bounds
+
+
+def bar_cloud(world, seed=SEED):
+    """the whole bar of `world` blocks as one cloud (the reference arm of bench.py --gpus N runs it on the host cores)"""
+    parts = [bar_block(r, world, seed) for r in range(world)]
+    return {k: np.concatenate([p[k] for p in parts]) for k in parts[0]}
+
+
 def workload(name, ppc=8, seed=SEED):
     n_grid, extent, lo, cn, dt = WORKLOADS[name]
     cloud = make_cloud(n_grid, extent, lo, cn, ppc=ppc, seed=seed)

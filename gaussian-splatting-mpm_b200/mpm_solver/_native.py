@@ -13,7 +13,7 @@ _ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB_PATH = os.environ.get("MPMK_LIB") or os.path.join(_ROOT, "lib", "libmpmk.so")
 
 MAT_JELLY, MAT_METAL, MAT_SAND, MAT_FOAM, MAT_FLUID, MAT_PLASTICINE = range(6)
-STRICT_Q1, STRICT_Q3, WRITE_FTRIAL, TRACK_COV, SORT_FULL, FUSE_G2P2G, SORT_MERGE = 1, 2, 4, 8, 16, 32, 64
+STRICT_Q1, STRICT_Q3, WRITE_FTRIAL, TRACK_COV, SORT_FULL, SORT_MERGE = 1, 2, 4, 8, 16, 64
 OP_FIXED_CUBE, OP_COLLIDER = 0, 1
 MAX_GRID_OPS, MAX_IMPULSES = 16, 8
 
@@ -106,6 +106,7 @@ def lib():
         "mpmk_particle_volume": (i, [vp, i64, vp, f, vp, vp, vp]),
         "mpmk_compute_keys": (i, [vp, vp]),
         "mpmk_constitutive": (i, [vp, f, vp]),
+        "mpmk_constitutive_ex": (i, [vp, f, i, i, vp]),
         "mpmk_sort": (i, [vp, vp]),
         "mpmk_get_sort_result": (i, [vp, vp, vp, vp]),
         "mpmk_sort_info": (i, [vp, C.POINTER(i), C.POINTER(i64), vp]),

@@ -64,6 +64,11 @@ class _Backend:
         self.export_fresh = False     # out_* hold postprocess() results of the current state
         self._ftrial_valid = False
         self.cov_from_postprocess = False
+        # The library evaluates compute_stress_from_F_trial for substep s+1 in the g2p epilogue of substep s; the
+        # reference evaluates it at the start of substep s+1 (solver.py:36) with whatever was written to the model in
+        # between.  Writes that the update depends on mark it stale; the next substep redoes it first (flush_stress).
+        self.pristine = True          # F = I everywhere and no substep yet: the update is the identity, stress = 0
+        self.stress_dirty = None      # None | {"use_ft": bool, "use_ys_before": bool}
 
     # -- plumbing -------------------------------------------------------------------------
     def _bind(self):
@@ -106,6 +111,33 @@ class _Backend:
     def invalidate(self):
         self.export_fresh = False
         self.cov_from_postprocess = False
+
+    def mark_stress_dirty(self, f_written=False, ys_written=False):
+        """a write the constitutive update depends on (mu, lam, material, yield_stress, F, the scalar model
+        parameters): redo the update before the next substep, from the stored F_trial / pre-return-map yield stress
+        where the library still has them, so that the result is what the reference computes at the start of p2g2p"""
+        self.invalidate()
+        if f_written:
+            self.pristine = False
+            if self._ftrial_valid:   # the stored F_trial describes a state the caller has just replaced
+                self.ctx.call("mpmk_set_count", self.n, self.ctx.L.mpmk_current_set(self.ctx.h))
+                self._ftrial_valid = False
+        elif self.pristine:
+            return
+        d = self.stress_dirty or {"use_ft": True, "use_ys_before": True}
+        if f_written:
+            d["use_ft"] = False
+            d["use_ys_before"] = False
+        if ys_written:
+            d["use_ys_before"] = False
+        self.stress_dirty = d
+
+    def flush_stress(self, dt):
+        d = self.stress_dirty
+        if d is not None:
+            self.ctx.call("mpmk_constitutive_ex", float(dt), int(d["use_ft"]), int(d["use_ys_before"]), _stream())
+            self.stress_dirty = None
+        self.pristine = False
 
     def ftrial_valid(self):
         return self._ftrial_valid
@@ -365,7 +397,7 @@ class MPM_model:
         if args_material < 0:
             raise TypeError("Material not supported yet")
         self.gravity = tuple(float(g) for g in self.args.gravity)
-        self.material = _MaterialField(b, [("meta", 1)], (), dtype=torch.int32, after_write=b.invalidate)
+        self.material = _MaterialField(b, [("meta", 1)], (), dtype=torch.int32, after_write=b.mark_stress_dirty)
         self._args_material = args_material
         b.reset_order()
         b.sets[0]["meta"][: b.n, 1] = args_material
@@ -378,8 +410,8 @@ class MPM_model:
         self._y = torch.full((n,), -math.log(0.49 / self.args.nu - 1), dtype=torch.float32, device=dev)
         self.logE = PlainField(self._logE)
         self.y = PlainField(self._y)
-        self.mu = FieldView(b, [("f2", 1)], (), after_write=b.invalidate)
-        self.lam = FieldView(b, [("f2", 2)], (), after_write=b.invalidate)
+        self.mu = FieldView(b, [("f2", 1)], (), after_write=b.mark_stress_dirty)
+        self.lam = FieldView(b, [("f2", 2)], (), after_write=b.mark_stress_dirty)
         self.viscosity = PlainField(torch.full((n,), float(getattr(self.args, "viscosity", 0.05)), dtype=torch.float32, device=dev))
         self.recompute_mu_lam()
 
@@ -410,7 +442,7 @@ class MPM_model:
 
     def init_other_params(self):  # model.py:53-59
         b = self._backend
-        self.yield_stress = FieldView(b, [("f2", 3)], (), after_write=b.invalidate)
+        self.yield_stress = FieldView(b, [("f2", 3)], (), after_write=lambda: b.mark_stress_dirty(ys_written=True))
         self.yield_stress.fill(0.005)
         self.hardening = 1
         self.xi = 1
@@ -464,8 +496,9 @@ class MPM_state:
         self._xyz_packed = FieldView(b, [("xm", 0), ("xm", 1), ("xm", 2)], (3,), after_write=b.recompute_keys)
         self.particle_xyz = _ExportField(b, "xyz", self._xyz_packed)
         self.particle_vel = FieldView(b, [("vv", 0), ("vv", 1), ("vv", 2)], (3,), after_write=inval)
-        self.particle_F = FieldView(b, F, (3, 3), after_write=inval)
-        self.particle_stress = _SymStressField(b, S6, (3, 3), after_write=inval)
+        self.particle_F = FieldView(b, F, (3, 3), after_write=lambda: b.mark_stress_dirty(f_written=True))
+        # (the reference overwrites particle_stress from F_trial at the start of every p2g2p, utils.py:14-54)
+        self.particle_stress = _SymStressField(b, S6, (3, 3), after_write=b.mark_stress_dirty)
         self.particle_C = FieldView(b, Cc, (3, 3), after_write=inval)
         self.particle_pressure = PlainField(torch.zeros(max(n, 1), dtype=torch.float32, device=dev))
         self.particle_init_cov = PlainField(b.init_cov.view(-1), after_write=inval)
@@ -511,6 +544,8 @@ class MPM_state:
         cur["cv0"][:n] = c6[:, :4]
         cur["cv1"][:n, :2] = c6[:, 4:]
         b._ftrial_valid = False
+        b.pristine = True
+        b.stress_dirty = None
         b.invalidate()
         b.recompute_keys()
 

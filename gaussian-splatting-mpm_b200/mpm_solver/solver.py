@@ -65,7 +65,6 @@ class MPM_Simulator:
         self._strict_q3 = strict_q3
         self._track_cov = track_cov
         self._sort_full = False
-        self._fuse_g2p2g = False
         self._sort_merge = False
         self._sync_flags()
 
@@ -99,8 +98,6 @@ class MPM_Simulator:
             f |= _native.TRACK_COV
         if self._sort_full:
             f |= _native.SORT_FULL
-        if self._fuse_g2p2g:
-            f |= _native.FUSE_G2P2G
         if self._sort_merge:
             f |= _native.SORT_MERGE
         if self._has_plastic():
@@ -112,8 +109,8 @@ class MPM_Simulator:
         """Update solver parameters from a dict (not in the reference; north_star asks for it).
         Keys: gravity, E, nu, yield_stress, hardening, xi, plastic_viscosity, softening, friction_angle,
         strict_q1, strict_q3, track_cov, sort_full (always the full radix sort, never the merge of the movers), sort_merge (the merge whenever valid,
-        also for small clouds), fuse_g2p2g (step() runs the gather of one
-        substep and the scatter of the next as one kernel)."""
+        also for small clouds).  The physics keys take effect from the next substep on, as they would in the reference, whose
+        p2g2p re-evaluates the stress from F_trial with the current parameters (solver.py:36)."""
         p = dict(params or {})
         p.update(kw)
         m = self.mpm_model
@@ -132,12 +129,14 @@ class MPM_Simulator:
                 m._logE.fill_(math.log10(v))
             elif k == "nu":
                 m._y.fill_(-math.log(0.49 / v - 1))
-            elif k in ("strict_q1", "strict_q3", "track_cov", "sort_full", "fuse_g2p2g", "sort_merge"):
+            elif k in ("strict_q1", "strict_q3", "track_cov", "sort_full", "sort_merge"):
                 setattr(self, "_" + k, bool(v))
             else:
                 raise KeyError(k)
         if "E" in p or "nu" in p:
             m.recompute_mu_lam()
+        if any(k in p for k in ("hardening", "xi", "plastic_viscosity", "softening", "friction_angle", "strict_q1", "strict_q3")):
+            self._backend.mark_stress_dirty()
         self._sync_flags()
 
     set_parameters_dict = set_parameters
@@ -167,6 +166,7 @@ class MPM_Simulator:
     def p2g2p(self, dt):
         b = self._backend
         ops = self._ops_at(self.time)
+        b.flush_stress(dt)
         b.ctx.call("mpmk_substep", float(dt), C.byref(ops), _stream())
         b._ftrial_valid = bool(b.params.flags & _native.WRITE_FTRIAL)
         b.invalidate()
@@ -178,6 +178,8 @@ class MPM_Simulator:
         as the reference's loop (solver.py:52), so activity windows switch on the same substeps."""
         b = self._backend
         dt = float(self.mpm_model.args.substep_dt if dt is None else dt)
+        if n_substeps > 0:
+            b.flush_stress(dt)
         i = 0
         while i < n_substeps:
             ops = self._ops_at(self.time)

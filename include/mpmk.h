@@ -52,8 +52,6 @@ extern "C" {
 #define MPMK_STRICT_Q3 2u  /* constitutive_models.py:256: foam F through Hadamard     */
 #define MPMK_WRITE_FTRIAL 4u /* g2p also stores F_trial (needed by export for plastic)  */
 #define MPMK_TRACK_COV 8u  /* g2p applies update_cov every substep (utils.py:187-215) */
-#define MPMK_FUSE_G2P2G 32u /* mpmk_substeps: run the g2p of substep i and the p2g of substep i+1 as one kernel
-                            * (csrc/g2p2g.cu; halves particle traffic, measured no faster on B200: DESIGN.md 7) */
 #define MPMK_SORT_MERGE 64u /* take the merge path whenever it is valid, also below the size where it pays (tests) */
 #define MPMK_SORT_FULL 16u /* always run the full radix sort (no merge of the few particles that changed cell) */
 
@@ -81,7 +79,7 @@ typedef struct {
 
 typedef struct {
     mpmk_particle_set set[2];
-    void* ft0;      /* float4 x3: F_trial of the last g2p, sorted order (model.py:98) */
+    void* ft0;      /* float4 x3: F_trial of the last g2p, sorted order (model.py:98); ft2 = {Ft22, yield_stress before the return map, 0, 0} */
     void* ft1;
     void* ft2;
     void* keys;     /* uint32[capacity]: cell key of the particle in each physical slot */
@@ -161,6 +159,13 @@ MPMK_API int mpmk_compute_keys(mpmk_ctx* ctx, void* stream);
 /* utils.py:14-54 compute_stress_from_F_trial on the current set, in place:
  * F <- return_map(F), stress <- tau(F).  Used after init / from_torch edits. */
 MPMK_API int mpmk_constitutive(mpmk_ctx* ctx, float dt, void* stream);
+/* The library evaluates compute_stress_from_F_trial for substep s+1 in the epilogue of substep s's g2p, with the
+ * per-particle parameters of that moment; the reference evaluates it at the START of substep s+1 (solver.py:36), i.e.
+ * with whatever the caller wrote to mu / lam / yield_stress / material / the scalar parameters in between.  After such a
+ * write the host layer calls this to redo the update: use_ftrial != 0 takes F_trial from the stored ft0..ft2 (valid after
+ * a g2p with MPMK_WRITE_FTRIAL) instead of the already return-mapped F; use_ys_before != 0 takes the yield stress as it
+ * was BEFORE that g2p's return map (ft2.y), so hardening / softening is applied once, not twice.                    */
+MPMK_API int mpmk_constitutive_ex(mpmk_ctx* ctx, float dt, int use_ftrial, int use_ys_before, void* stream);
 
 /* ---- the substep, stage by stage (solver.py:27-52) ------------------------ */
 /* stable sort of (key, slot) by key; results stay in library scratch.  Full LSD radix sort, or -- when the

@@ -727,6 +727,15 @@ ORC_API void orc_reset_grid(int n_grid, float* grid_mass, float* grid_v_in, floa
     memset(grid_v_out, 0, 3 * G * sizeof(float));
 }
 
+/* bench.py: torchrun exports OMP_NUM_THREADS=1 to its workers; the timed CPU arm asks for the cores it may use */
+ORC_API void orc_set_num_threads(int n) {
+#if defined(_OPENMP) && defined(ORC_OMP)
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 ORC_API int orc_num_threads(void) {
 #if defined(_OPENMP) && defined(ORC_OMP)
     return omp_get_max_threads();

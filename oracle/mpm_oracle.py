@@ -69,6 +69,8 @@ def lib(omp: bool = False):
     L.orc_particle_volume.argtypes = [i, _fp, i, f, _fp]
     L.orc_reset_grid.argtypes = [i, _fp, _fp, _fp]
     L.orc_num_threads.restype = i
+    L.orc_set_num_threads.argtypes = [i]
+    L.orc_set_num_threads.restype = None
     for name in dir(L):
         pass
     _libs[omp] = L
@@ -224,8 +226,8 @@ class OracleSim:
                     self.L.orc_compute_mu_lam_from_E_nu(self.n_particles, self.logE, self.y, self.mu, self.lam)
                     if a["mu"] != 1000:
                         self.mu[inside] = np.float32(a["mu"])
-                    self.L.orc_compute_mass_from_vol_density(self.n_particles, self.particle_density,
-                                                             self.particle_vol, self.particle_mass)
+                    # boundary_conditions.py:62 only assigns particle_density; particle_mass was computed in
+                    # MPM_state.__init__ (model.py:107) and is NOT recomputed -- the override never reaches the mass
 
     def add_surface_collider(self, point, normal, surface="sticky", friction=0.0, start_time=0.0, end_time=999.0):
         s = 1.0 / math.sqrt(float(sum(x ** 2 for x in normal)))

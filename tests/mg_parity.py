@@ -22,7 +22,7 @@ from mpm_solver.solver import MPM_Simulator  # noqa: E402
 TOL_X, TOL_F = 1e-4, 1e-4   # max|dx| / grid dx ; relative Frobenius error of cov (F Sigma0 F^T)
 
 
-def run_case(material, S, rank, world, dev, omega, ghost=1, migrate_every=5):
+def run_case(material, S, rank, world, dev, omega, ghost=1, migrate_every=5, out=sys.stdout):
     n_grid, lo, cn, dt = 64, (22, 22, 22), (20, 20, 20), 4e-4
     if world > 2:   # at least 8 planes per slab (a slab must be >= 2*ghost+2 planes thick)
         cn = (8 * world, 16, 16)
@@ -56,6 +56,7 @@ def run_case(material, S, rank, world, dev, omega, ghost=1, migrate_every=5):
     dist.all_reduce(moved)
     ok = True
     msg = ""
+    res = {"ranks": world, "particles": N, "substeps": S, "material": material, "migrated": int(moved.item())}
     if rank == 0:
         one = MPM_Simulator(t(cloud["xyz"]), t(cloud["cov"]), t(cloud["vol"]), args, strict_q1=False)
         one.mpm_state.particle_vel.from_torch(t(cloud["vel"]))
@@ -81,11 +82,14 @@ def run_case(material, S, rank, world, dev, omega, ghost=1, migrate_every=5):
         msg = (f"{material}: N={N} ranks={world} S={S} migrated={int(moved.item())} counts={[int(c.item()) for c in cnts]} "
                f"vs 1 GPU: max|dx|/dx={ex:.2e} rel cov={ec:.2e}; vs oracle: {exo:.2e} {eco:.2e}")
         ok = ex < TOL_X and ec < TOL_F and exo < TOL_X and eco < TOL_F and int(moved.item()) > 0
-        print(msg, flush=True)
+        res.update({"max_dx_over_dx": max(ex, exo), "rel_cov": max(ec, eco), "vs_one_gpu": [ex, ec], "vs_oracle": [exo, eco],
+                    "halo_path": sl.halo_path})
+        print(msg, file=out, flush=True)
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.broadcast(flag, src=0)
     sl.close()
-    return bool(flag.item())
+    res["ok"] = bool(flag.item())
+    return res
 
 
 def main():
@@ -96,7 +100,7 @@ def main():
     ok = True
     for material, S, omega, ghost, every in (("jelly", 40, (0.0, 0.0, 20.0), 1, 5), ("sand", 20, (0.0, 0.0, 20.0), 1, 5),
                                              ("metal", 30, (0.0, 0.0, 20.0), 2, "auto")):
-        ok = run_case(material, S, rank, world, dev, omega, ghost, every) and ok
+        ok = run_case(material, S, rank, world, dev, omega, ghost, every)["ok"] and ok
     dist.barrier()
     if rank == 0:
         print("mg parity ok" if ok else "mg parity FAILED", flush=True)

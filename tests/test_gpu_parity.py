@@ -271,51 +271,6 @@ def test_coherent_sort_equals_full_sort_trajectory(cuda_dev):
     assert rel_fro(ca.cpu().numpy(), cb.cpu().numpy()) < 5e-5
 
 
-@pytest.mark.parametrize("material,omega,dt", [
-    ("jelly", (0.0, 0.0, 2.0), 4e-4),
-    ("jelly", (3.0, -4.0, 40.0), 4e-4),     # fast: several per cent of the particles leave their tile every substep
-    ("metal", (3.0, -4.0, 40.0), 4e-4),
-    ("sand", (0.0, 0.0, 2.0), 4e-4),
-])
-def test_fused_g2p2g_equals_unfused(cuda_dev, material, omega, dt):
-    """With fuse_g2p2g, step(n) fuses the gather of substep i with the scatter of substep i+1 (csrc/g2p2g.cu).  Per particle the
-    arithmetic is that of the two stand-alone kernels; only the order of a node's float additions differs.  Checked
-    against the same batches with fusion off, and against the oracle with the usual tolerances."""
-    n_grid, lo, cn = 64, (22, 22, 22), (20, 20, 20)
-    cloud = synthetic.make_cloud(n_grid, 2.0, lo, cn, seed=5, omega=omega)
-    args = synthetic.sim_args(n_grid=n_grid, material=material, substep_dt=dt)
-    ops = synthetic.block_ops(n_grid, 2.0, lo, cn)
-    ops["boundary_conditions"].append({"id": 7, "type": "impulse", "center": [1.0, 1.0, 1.0], "size": [0.2, 0.2, 0.2],
-                                       "force": [0.0, 0.5, -1.0], "start_time": 2 * dt, "num_dt": 9})
-    a = make_gpu(cloud, args, cuda_dev, ops, strict_q1=False)
-    b = make_gpu(cloud, args, cuda_dev, ops, strict_q1=False)
-    a.set_parameters(fuse_g2p2g=True)
-    o = make_oracle(cloud, args, ops, strict_q1=False)
-    S = 20
-    for chunk in (7, 1, 12):
-        a.step(chunk, dt); b.step(chunk, dt)
-    for _ in range(S):
-        o.p2g2p(dt)
-    assert abs(a.time - b.time) < 1e-12 and abs(a.time - o.time) < 1e-12
-    assert np.array_equal(a._backend.ids().cpu().numpy(), b._backend.ids().cpu().numpy())
-    xa, ca, _ = a.export(); xb, cb, _ = b.export()
-    dx = 2.0 / n_grid
-    # the two schedules add the same terms in different orders (and the float atomics make each of them vary from run
-    # to run); the plastic return maps amplify that noise over the 20 substeps, so the bounds are SURVEY.md 8c's
-    # stated ones, not a few ulp (observed: 2e-5 * dx, 3e-6, 5e-6; grids 1e-5 .. 5.4e-5)
-    assert (xa - xb).abs().max().item() < 1e-4 * dx
-    assert rel_fro(ca.cpu().numpy(), cb.cpu().numpy()) < 1e-4
-    va = a.mpm_state.particle_vel.to_torch().cpu().numpy(); vb = b.mpm_state.particle_vel.to_torch().cpu().numpy()
-    assert rel_fro(va, vb) < 1e-4
-    o.postprocess()
-    assert np.abs(xa.cpu().numpy() - o.in_original_order("particle_xyz")).max() < 1e-4 * dx
-    assert rel_fro(ca.cpu().numpy().reshape(-1), np.asarray(o.in_original_order("particle_cov")).reshape(-1)) < 1e-4
-    # the grid fields hold the last substep's scatter and update, as after a loop of p2g2p() calls
-    ga = a._backend.grid_in.cpu().numpy(); gb = b._backend.grid_in.cpu().numpy()
-    assert rel_fro(ga, gb) < 2e-4
-    assert rel_fro(a._backend.grid_out.cpu().numpy(), b._backend.grid_out.cpu().numpy()) < 2e-4
-
-
 def test_substeps_graph_equals_loop(cuda_dev):
     cloud, args = small_cloud(n_grid=40, cells_lo=(12, 12, 12), cells_n=(8, 8, 8), material="metal")
     ops = synthetic.block_ops(40, 2.0, (12, 12, 12), (8, 8, 8))
