@@ -63,8 +63,11 @@ def test_config_shaped_parity(cuda_dev, name, S, stride):
     e = _compare(g, o)
     if name != "bicycle-like":   # the plastic models must have yielded somewhere (hardening / softening moved the yield
         assert (o.yield_stress != np.float32(0.005)).mean() > 0.01, "no return mapping fired"   # stress), or the test says nothing about them
+        # sigma_y accumulates the plastic multipliers, each a difference of nearly equal numbers (|eps_dev| - sigma_y / 2 mu):
+        # 1e-2 per particle, 1e-3 on average
         ys = g.mpm_model.yield_stress.to_torch().cpu().numpy()
-        assert np.allclose(ys, o.in_original_order("yield_stress"), rtol=2e-3, atol=1e-6)
+        ys_o = o.in_original_order("yield_stress")
+        assert np.allclose(ys, ys_o, rtol=1e-2, atol=1e-6) and np.abs(ys - ys_o).mean() < 1e-3 * 0.005
     print(name, g.n_particles, e)
 
 
