@@ -32,7 +32,8 @@ struct DevCounters {
     uint32_t n_clamped;
     uint32_t p2g_cursor;   // dynamic work fetch
     uint32_t g2p_cursor;
-    uint32_t pad[2];
+    uint32_t n_cross;      // lagged batches: particles whose cell left their work item's tile (g2p defers them to k_g2p_cross)
+    uint32_t list_stamp;   // lagged batches: stamp value of the block list this work list goes with
 };
 
 // multi-GPU slab state (mg.cu)
@@ -65,6 +66,7 @@ struct mpmk_ctx {
     int key_bits;
     int sm_count;
     int g2p_ctas_per_sm, p2g_ctas_per_sm;  // occupancy-derived persistent grid sizes
+    int p2g_lag_ctas_per_sm;
     // fused batches (g2p2g.cu): the next substep's scatter is already in grid_in when the substep starts, so the
     // clear must leave grid_in alone, and the grid pass zeroes grid_in behind itself for the scatter that follows it
     bool keep_grid_in, zero_grid_in;
@@ -88,37 +90,52 @@ struct mpmk_ctx {
     uint32_t* sort_ctrl;     // one-sweep control block: tile counters, digit histograms, status words (sort.cu)
     uint32_t* hist_tot;      // 2048 words: the 1024 evenly spaced old keys the coherent sort searches first
     int64_t n_sort_ctas_cap;
-    uint4* items;            // {begin, count, tile, 0}
+    // work list, double-buffered: p2g / g2p consume set [wl]; prepare builds into [1-wl] and flips.  In a lagged batch
+    // (api.cu) the sort + prepare of substep s run on a side branch while p2g / grid of substep s still consume set [wl].
+    uint4* items_buf[2];     // {begin, count, tile, 0}
+    DevCounters* counters_buf[2];
+    int wl;
+    uint4* items;            // == items_buf[wl]
+    DevCounters* counters;   // == counters_buf[wl]
     uint2* tile_list;        // non-empty tiles of the current sort: {tile, first sorted index}
     uint32_t* tile_end;      // [nt^3] one past the last sorted index of each non-empty tile
     int64_t items_cap;
-    uint32_t* block_stamp;   // [nb^3]
+    uint32_t* block_stamp[2];// [nb^3] per block list (a lagged batch stamps list [cur_list] from p2g while the side branch builds the other)
     uint32_t* block_list[2]; // active node blocks: [cur_list] this substep, [1-cur_list] previous
     uint32_t* block_count[2];// device scalars
     int cur_list;
     uint32_t* dev_stamp;     // device scalar: substep stamp for block_stamp (device-side so graphs replay correctly)
-    DevCounters* counters;
+    // lagged batches (api.cu): the sort of substep s leaves the critical path
+    uint32_t* rank;          // inverse of perm: sorted position of each physical slot (g2p's destination slot)
+    uint32_t* keys_b;        // second key buffer: g2p reads the keys of its source slots while it writes the next ones
+    uint32_t* keys_cur;      // the buffer holding the current keys: b.keys at every API boundary, keys_b inside a batch
+    uint32_t* cross_list;    // physical slots of the particles g2p deferred (their cell lies outside the item's tile)
+    bool lag_ready;          // set [1-wl] / list [1-cur_list] are prebuilt for the current physical order, grid_in is clean
+    uint32_t* lag_done;      // device scalar: CTAs of k_lag_clear_out that have finished
+    unsigned long long* trace;  // MPMK_TRACE: %globaltimer stamps of the last lagged substep (api.cu)
+    cudaStream_t side_stream;
+    cudaEvent_t ev_fork, ev_clear, ev_join, ev_grid, ev_end;
     bool sorted_valid;       // sorted_keys/perm describe the current set
     bool prepared;           // work list built for the current sort
     bool ftrial_valid;
     int64_t launches;
     // CUDA graph cache for mpmk_substeps
+    struct HostState {
+        int cur, cur_list, wl;
+        bool coherent, lag_ready, last_sort_coherent;
+        uint32_t* sorted_keys;
+        uint32_t* keys_alt;
+    };
     struct GraphEntry {
         cudaGraphExec_t exec;
         float dt;
         mpmk_substep_ops ops;
         int n_steps;
-        int cur, cur_list;
         uint32_t flags;
         int64_t n;
         mpmk_bindings b;
-        bool coherent;            // state the capture started from ...
-        uint32_t* sorted_keys;
-        bool end_coherent;        // ... and the state it leaves behind
-        bool end_last_sort_coherent;
+        HostState start, end;     // state the capture started from / leaves behind
         int64_t kernels;          // kernel launches inside the graph (mpmk_launch_count counts them per replay)
-        uint32_t* end_sorted_keys;
-        uint32_t* end_keys_alt;
     } graphs[MPMK_GRAPH_CACHE];
     int n_graphs;
     cudaStream_t cap_stream;  // graphs are captured here (the legacy default stream cannot be captured)
@@ -258,6 +275,16 @@ struct BatchStream {
 int mpmk_launch_keys(mpmk_ctx* ctx, cudaStream_t s);
 int mpmk_launch_sort(mpmk_ctx* ctx, cudaStream_t s);
 int mpmk_launch_prepare(mpmk_ctx* ctx, cudaStream_t s);
+int mpmk_launch_prepare_lagged(mpmk_ctx* ctx, cudaStream_t s);
+int mpmk_launch_lag_clear_out(mpmk_ctx* ctx, cudaStream_t s);
+int mpmk_launch_lag_clear_in(mpmk_ctx* ctx, cudaStream_t s);
+int mpmk_worklist_init(mpmk_ctx* ctx);
+int mpmk_launch_lag_enter(mpmk_ctx* ctx, cudaStream_t s);
+int mpmk_launch_p2g_lagged(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);
+int mpmk_launch_grid_lagged(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);
+int mpmk_launch_g2p_lagged(mpmk_ctx* ctx, float dt, cudaStream_t s);
+int mpmk_launch_sort_lagged(mpmk_ctx* ctx, cudaStream_t s);
+void mpmk_lag_flip(mpmk_ctx* ctx);
 int mpmk_item_size(const mpmk_ctx* ctx);
 int mpmk_launch_p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);
 int mpmk_launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);

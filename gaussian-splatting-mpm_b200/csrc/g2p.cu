@@ -12,8 +12,8 @@
 #include "constitutive.cuh"
 
 struct G2PArgs {
-    const uint32_t* perm;
-    const uint32_t* skeys;
+    const uint32_t* perm;    // classic: source slot of sorted particle r.  LAG: rank, the destination slot of physical slot r
+    const uint32_t* skeys;   // classic: sorted keys.  LAG: the current keys, in physical order
     // source set
     const float4 *xm, *f0, *f1, *f2, *cv0, *cv1;
     const int4* meta;
@@ -25,6 +25,7 @@ struct G2PArgs {
     const uint4* items;
     const float4* grid_out;
     DevCounters* cnt;
+    uint32_t* cross;         // LAG: physical slots deferred to k_g2p_cross
     int64_t n;
     int n_grid, nt;
     float inv_dx, dt;
@@ -42,6 +43,132 @@ __device__ __forceinline__ void bspline(float f, float* w, float* dw) {
     dw[0] = f - 1.5f; dw[1] = -2.0f * (f - 1.0f); dw[2] = f - 0.5f;
 }
 
+// One particle: gather from the 3x3x3 nodes at g (x stride sx, y stride sy float4s: the warp's shared tile, or the
+// global grid for a crosser), then everything utils.py:255-279 and the next substep's utils.py:14-54 do with it.
+// src / dst: the particle's slot in the source / destination set; pF0..pMeta: its records (shared stage or global).
+__device__ __forceinline__ void g2p_particle(const G2PArgs& a, const uint32_t src, const uint32_t dst, const float4 X, const float fx,
+                                             const float fy, const float fz, const float4* __restrict__ g, const int sx, const int sy,
+                                             const float4* pF0, const float4* pF1, const float4* pF2, const int4* pMeta) {
+    const int n = a.n_grid;
+    const float dt = a.dt;
+    const float k4 = 4.0f * a.inv_dx;
+    // only w is kept live; dw (linear in f) and the APIC moment weights w_d (off_d - f_d), shifted per
+    // axis so no large terms cancel, are re-derived where they are used (register pressure)
+    float wx[3], wy[3], wz[3], dwz[3];
+    bspline_w(fx, wx); bspline_w(fy, wy); bspline_w(fz, wz);
+    dwz[0] = fz - 1.5f; dwz[1] = -2.0f * (fz - 1.0f); dwz[2] = fz - 0.5f;
+    const float wzd[3] = {wz[0] * (0.f - fz), wz[1] * (1.f - fz), wz[2] * (2.f - fz)};
+
+    // sums over the stencil: v, M_d = sum w (off_d - f_d) v (d=x,y,z), G_d = sum (dw_d-weighted) v
+    float v[3] = {0, 0, 0}, Mx[3] = {0, 0, 0}, My[3] = {0, 0, 0}, Mz[3] = {0, 0, 0};
+    float Gx[3] = {0, 0, 0}, Gy[3] = {0, 0, 0}, Gz[3] = {0, 0, 0};
+#pragma unroll 1
+    for (int i = 0; i < 3; ++i) {
+        float A[3] = {0, 0, 0}, Ay[3] = {0, 0, 0}, Gyi[3] = {0, 0, 0}, Az[3] = {0, 0, 0}, Gzi[3] = {0, 0, 0};
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            const float4* row = g + (i * sx + j * sy);
+            const float4 g0 = row[0], g1 = row[1], g2 = row[2];
+            // contraction along z
+            const float ax = wz[0] * g0.x + wz[1] * g1.x + wz[2] * g2.x;
+            const float ay = wz[0] * g0.y + wz[1] * g1.y + wz[2] * g2.y;
+            const float az = wz[0] * g0.z + wz[1] * g1.z + wz[2] * g2.z;
+            const float zx = wzd[0] * g0.x + wzd[1] * g1.x + wzd[2] * g2.x;  // sum_k wz_k (k - fz) v
+            const float zy = wzd[0] * g0.y + wzd[1] * g1.y + wzd[2] * g2.y;
+            const float zz = wzd[0] * g0.z + wzd[1] * g1.z + wzd[2] * g2.z;
+            const float dx_ = dwz[0] * g0.x + dwz[1] * g1.x + dwz[2] * g2.x;
+            const float dy_ = dwz[0] * g0.y + dwz[1] * g1.y + dwz[2] * g2.y;
+            const float dz_ = dwz[0] * g0.z + dwz[1] * g1.z + dwz[2] * g2.z;
+            // contraction along y
+            const float wj = wy[j], wjj = wy[j] * ((float)j - fy);
+            const float dj = (j == 0) ? fy - 1.5f : (j == 1) ? -2.0f * (fy - 1.0f) : fy - 0.5f;
+            A[0] += wj * ax; A[1] += wj * ay; A[2] += wj * az;
+            Ay[0] += wjj * ax; Ay[1] += wjj * ay; Ay[2] += wjj * az;
+            Gyi[0] += dj * ax; Gyi[1] += dj * ay; Gyi[2] += dj * az;
+            Az[0] += wj * zx; Az[1] += wj * zy; Az[2] += wj * zz;
+            Gzi[0] += wj * dx_; Gzi[1] += wj * dy_; Gzi[2] += wj * dz_;
+        }
+        // contraction along x
+        const float wi = (i == 0) ? wx[0] : (i == 1) ? wx[1] : wx[2], wii = wi * ((float)i - fx);
+        const float di = (i == 0) ? fx - 1.5f : (i == 1) ? -2.0f * (fx - 1.0f) : fx - 0.5f;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            v[c] += wi * A[c];
+            Mx[c] += wii * A[c];
+            Gx[c] += di * A[c];
+            My[c] += wi * Ay[c];
+            Gy[c] += wi * Gyi[c];
+            Mz[c] += wi * Az[c];
+            Gz[c] += wi * Gzi[c];
+        }
+    }
+    // utils.py:266-275: v, x, C = sum w v (x) (off - f) * 4 inv_dx
+    const float nx = X.x + dt * v[0], ny = X.y + dt * v[1], nz = X.z + dt * v[2];
+    a.oxm[dst] = make_float4(nx, ny, nz, X.w);
+    a.ovv[dst] = make_float4(v[0], v[1], v[2], 0.f);
+    bool cl = false;
+    const int kx = base_cell(nx, a.inv_dx, n, cl), ky = base_cell(ny, a.inv_dx, n, cl), kz = base_cell(nz, a.inv_dx, n, cl);
+    a.okeys[dst] = make_key(kx, ky, kz, a.nt);
+    if (cl) atomicAdd(&a.cnt->n_clamped, 1u);
+    a.oc0[dst] = make_float4(Mx[0] * k4, My[0] * k4, Mz[0] * k4, Mx[1] * k4);
+    a.oc1[dst] = make_float4(My[1] * k4, Mz[1] * k4, Mx[2] * k4, My[2] * k4);
+    const float C22 = Mz[2] * k4;
+    // grad v = sum v (x) dweight  (row = velocity component, column = derivative direction)
+    float gv[9];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        gv[3 * c + 0] = Gx[c] * a.inv_dx;
+        gv[3 * c + 1] = Gy[c] * a.inv_dx;
+        gv[3 * c + 2] = Gz[c] * a.inv_dx;
+    }
+    // F_trial = (I + dt grad v) F   (utils.py:276-279)
+    const float4 F0 = *pF0, F1 = *pF1, F2 = *pF2;
+    const float Fo[9] = {F0.x, F0.y, F0.z, F0.w, F1.x, F1.y, F1.z, F1.w, F2.x};
+    float Ft[9];
+#pragma unroll
+    for (int rr = 0; rr < 3; ++rr)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            float s = (rr == 0 ? 1.0f + dt * gv[0] : dt * gv[3 * rr + 0]) * Fo[c];
+            s += (rr == 1 ? 1.0f + dt * gv[4] : dt * gv[3 * rr + 1]) * Fo[3 + c];
+            s += (rr == 2 ? 1.0f + dt * gv[8] : dt * gv[3 * rr + 2]) * Fo[6 + c];
+            Ft[3 * rr + c] = s;
+        }
+    if (a.cp.flags & MPMK_WRITE_FTRIAL) {
+        a.ft0[dst] = make_float4(Ft[0], Ft[1], Ft[2], Ft[3]);
+        a.ft1[dst] = make_float4(Ft[4], Ft[5], Ft[6], Ft[7]);
+        a.ft2[dst] = make_float4(Ft[8], F2.w, 0.f, 0.f);   // F2.w: the yield stress before this substep's return map
+    }
+    if (a.cp.flags & MPMK_TRACK_COV) {
+        // update_cov, utils.py:187-215: cov += dt (grad_v cov + cov grad_v^T)
+        const float4 q0 = ldg4(a.cv0 + src), q1 = ldg4(a.cv1 + src);
+        const float cn[9] = {q0.x, q0.y, q0.z, q0.y, q0.w, q1.x, q0.z, q1.x, q1.y};
+        float o[9];
+#pragma unroll
+        for (int rr = 0; rr < 3; ++rr)
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                float s1 = gv[3 * rr] * cn[c] + gv[3 * rr + 1] * cn[3 + c] + gv[3 * rr + 2] * cn[6 + c];
+                float s2 = cn[3 * rr] * gv[3 * c] + cn[3 * rr + 1] * gv[3 * c + 1] + cn[3 * rr + 2] * gv[3 * c + 2];
+                o[3 * rr + c] = cn[3 * rr + c] + dt * (s1 + s2);
+            }
+        a.ocv0[dst] = make_float4(o[0], o[1], o[2], o[4]);
+        a.ocv1[dst] = make_float4(o[5], o[8], 0.f, 0.f);
+    }
+    const int4 meta = *pMeta;
+    a.ometa[dst] = meta;
+    // constitutive update for the next substep
+    float mu = F2.y, lam = F2.z, ys = F2.w;
+    float Fn[9], s6[6];
+    constitutive_update(Ft, meta.y, mu, lam, ys, dt, a.cp, Fn, s6);
+    const float vol = __int_as_float(meta.z);
+    a.ocs[dst] = make_float4(C22, s6[0], s6[1], s6[2]);
+    a.os1[dst] = make_float4(s6[3], s6[4], s6[5], vol);
+    a.of0[dst] = make_float4(Fn[0], Fn[1], Fn[2], Fn[3]);
+    a.of1[dst] = make_float4(Fn[4], Fn[5], Fn[6], Fn[7]);
+    a.of2[dst] = make_float4(Fn[8], mu, lam, ys);
+}
+
 // One warp per work item (<= MPMK_ITEM_MAX sorted particles of one 4x4x4-cell tile).  The 6x6x6 nodes the
 // tile's stencils reach are staged in the warp's shared-memory tile; lanes = particles gather from it
 // in batches of 32.  The kernel is latency-bound unless every warp keeps global loads in flight while it
@@ -53,6 +180,11 @@ __device__ __forceinline__ void bspline(float f, float* w, float* dw) {
 //     batch A: gather + C/F update + constitutive update + stores
 // 4 warps x 5 CTAs per SM: 20 warps at <= 102 registers each.  Measured on S-4M (jelly): 8x3 (cap 85, spills)
 // 0.288 ms, 4x6 (cap 85) 0.291, 4x4 (cap 128) 0.305, 2x9 0.262, 4x5 = 2x10 0.221.
+//
+// LAG = true (lagged batches, api.cu): the work list comes from the sort of the previous substep, batches are 32
+// consecutive physical slots, the true cell comes from the current key, and the particle is written to the slot the
+// sort of THIS substep (done on the side branch by now) ranks it at.  Particles whose cell left the item's tile are
+// handed to k_g2p_cross, which gathers from the global grid.
 #ifndef G2P_WARPS
 #define G2P_WARPS 4
 #endif
@@ -64,10 +196,11 @@ __device__ __forceinline__ void bspline(float f, float* w, float* dw) {
 struct __align__(16) G2PWarpSmem {
     float4 rec[2][G2P_NREC][32];
     float4 tile[MPMK_TILE_NODES];
-    uint32_t perm[2][32];  // permutation entries of batches B/C (ring), kept out of registers
+    uint32_t perm[2][32];  // permutation (LAG: rank) entries of batches B/C (ring), kept out of registers
     uint32_t key[3][32];   // keys of batches A/B/C (ring)
 };
 
+template <bool LAG>
 __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PArgs a) {
     pdl_wait();   // programmatic dependent launch: nothing of the previous grid is read or overwritten before this
     extern __shared__ float4 g2p_smem_raw[];
@@ -75,8 +208,6 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
     const int lane = threadIdx.x & 31;
     G2PWarpSmem& S = reinterpret_cast<G2PWarpSmem*>(g2p_smem_raw)[warp];
     const int n = a.n_grid;
-    const float dt = a.dt;
-    const float k4 = 4.0f * a.inv_dx;
 
     BatchStream bs;
     bs.init();
@@ -91,11 +222,12 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
     if (lane < dA.count) {
         pA = a.perm[dA.base + lane];
         S.key[0][lane] = a.skeys[dA.base + lane];
-        cp_async16(&S.rec[0][0][lane], a.xm + pA);
-        cp_async16(&S.rec[0][1][lane], a.f0 + pA);
-        cp_async16(&S.rec[0][2][lane], a.f1 + pA);
-        cp_async16(&S.rec[0][3][lane], a.f2 + pA);
-        cp_async16(&S.rec[0][4][lane], a.meta + pA);
+        const uint32_t sA = LAG ? dA.base + lane : pA;
+        cp_async16(&S.rec[0][0][lane], a.xm + sA);
+        cp_async16(&S.rec[0][1][lane], a.f0 + sA);
+        cp_async16(&S.rec[0][2][lane], a.f1 + sA);
+        cp_async16(&S.rec[0][3][lane], a.f2 + sA);
+        cp_async16(&S.rec[0][4][lane], a.meta + sA);
     }
     BatchDesc dB = bs.next(lane, a.items, &a.cnt->g2p_cursor, n_items);
     if (lane < dB.count) {
@@ -121,11 +253,12 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
         uint32_t pB = 0;
         if (lane < dB.count) {
             pB = S.perm[pslot][lane];
-            cp_async16(&S.rec[stage ^ 1][0][lane], a.xm + pB);
-            cp_async16(&S.rec[stage ^ 1][1][lane], a.f0 + pB);
-            cp_async16(&S.rec[stage ^ 1][2][lane], a.f1 + pB);
-            cp_async16(&S.rec[stage ^ 1][3][lane], a.f2 + pB);
-            cp_async16(&S.rec[stage ^ 1][4][lane], a.meta + pB);
+            const uint32_t sB = LAG ? dB.base + lane : pB;
+            cp_async16(&S.rec[stage ^ 1][0][lane], a.xm + sB);
+            cp_async16(&S.rec[stage ^ 1][1][lane], a.f0 + sB);
+            cp_async16(&S.rec[stage ^ 1][2][lane], a.f1 + sB);
+            cp_async16(&S.rec[stage ^ 1][3][lane], a.f2 + sB);
+            cp_async16(&S.rec[stage ^ 1][4][lane], a.meta + sB);
         }
         const BatchDesc dC = bs.next(lane, a.items, &a.cnt->g2p_cursor, n_items);
         const int kslotC = (kslot + 2) % 3;
@@ -140,131 +273,17 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
         if (lane < dA.count) {
             const uint32_t r = dA.base + lane;
             const uint32_t key = S.key[kslot][lane];
-            const float4 X = S.rec[stage][0][lane];
-            const int lx = (key >> 4) & 3, ly = (key >> 2) & 3, lz = key & 3;
-            const float fx = __fmul_rn(X.x, a.inv_dx) - (float)(4 * tx + lx);
-            const float fy = __fmul_rn(X.y, a.inv_dx) - (float)(4 * ty + ly);
-            const float fz = __fmul_rn(X.z, a.inv_dx) - (float)(4 * tz + lz);
-            // only w is kept live; dw (linear in f) and the APIC moment weights w_d (off_d - f_d), shifted per
-            // axis so no large terms cancel, are re-derived where they are used (register pressure)
-            float wx[3], wy[3], wz[3], dwz[3];
-            bspline_w(fx, wx); bspline_w(fy, wy); bspline_w(fz, wz);
-            dwz[0] = fz - 1.5f; dwz[1] = -2.0f * (fz - 1.0f); dwz[2] = fz - 0.5f;
-            const float wzd[3] = {wz[0] * (0.f - fz), wz[1] * (1.f - fz), wz[2] * (2.f - fz)};
-
-            // sums over the stencil: v, M_d = sum w (off_d - f_d) v (d=x,y,z), G_d = sum (dw_d-weighted) v
-            float v[3] = {0, 0, 0}, Mx[3] = {0, 0, 0}, My[3] = {0, 0, 0}, Mz[3] = {0, 0, 0};
-            float Gx[3] = {0, 0, 0}, Gy[3] = {0, 0, 0}, Gz[3] = {0, 0, 0};
-            const float4* g = S.tile + (lx * 36 + ly * 6 + lz);
-#ifdef EXP_NOGATHER
-            { const float4 g0 = g[0]; v[0] = g0.x; v[1] = g0.y; v[2] = g0.z; Mx[0] = fx; My[1] = fy; Mz[2] = fz; Gx[0] = wx[0]; Gy[1] = wy[1]; Gz[2] = wz[2] + wzd[0] + dwz[1]; }
-#else
-#pragma unroll 1
-            for (int i = 0; i < 3; ++i) {
-                float A[3] = {0, 0, 0}, Ay[3] = {0, 0, 0}, Gyi[3] = {0, 0, 0}, Az[3] = {0, 0, 0}, Gzi[3] = {0, 0, 0};
-#pragma unroll
-                for (int j = 0; j < 3; ++j) {
-                    const float4* row = g + (i * 36 + j * 6);
-                    const float4 g0 = row[0], g1 = row[1], g2 = row[2];
-                    // contraction along z
-                    const float ax = wz[0] * g0.x + wz[1] * g1.x + wz[2] * g2.x;
-                    const float ay = wz[0] * g0.y + wz[1] * g1.y + wz[2] * g2.y;
-                    const float az = wz[0] * g0.z + wz[1] * g1.z + wz[2] * g2.z;
-                    const float zx = wzd[0] * g0.x + wzd[1] * g1.x + wzd[2] * g2.x;  // sum_k wz_k (k - fz) v
-                    const float zy = wzd[0] * g0.y + wzd[1] * g1.y + wzd[2] * g2.y;
-                    const float zz = wzd[0] * g0.z + wzd[1] * g1.z + wzd[2] * g2.z;
-                    const float dx_ = dwz[0] * g0.x + dwz[1] * g1.x + dwz[2] * g2.x;
-                    const float dy_ = dwz[0] * g0.y + dwz[1] * g1.y + dwz[2] * g2.y;
-                    const float dz_ = dwz[0] * g0.z + dwz[1] * g1.z + dwz[2] * g2.z;
-                    // contraction along y
-                    const float wj = wy[j], wjj = wy[j] * ((float)j - fy);
-                    const float dj = (j == 0) ? fy - 1.5f : (j == 1) ? -2.0f * (fy - 1.0f) : fy - 0.5f;
-                    A[0] += wj * ax; A[1] += wj * ay; A[2] += wj * az;
-                    Ay[0] += wjj * ax; Ay[1] += wjj * ay; Ay[2] += wjj * az;
-                    Gyi[0] += dj * ax; Gyi[1] += dj * ay; Gyi[2] += dj * az;
-                    Az[0] += wj * zx; Az[1] += wj * zy; Az[2] += wj * zz;
-                    Gzi[0] += wj * dx_; Gzi[1] += wj * dy_; Gzi[2] += wj * dz_;
-                }
-                // contraction along x
-                const float wi = (i == 0) ? wx[0] : (i == 1) ? wx[1] : wx[2], wii = wi * ((float)i - fx);
-                const float di = (i == 0) ? fx - 1.5f : (i == 1) ? -2.0f * (fx - 1.0f) : fx - 0.5f;
-#pragma unroll
-                for (int c = 0; c < 3; ++c) {
-                    v[c] += wi * A[c];
-                    Mx[c] += wii * A[c];
-                    Gx[c] += di * A[c];
-                    My[c] += wi * Ay[c];
-                    Gy[c] += wi * Gyi[c];
-                    Mz[c] += wi * Az[c];
-                    Gz[c] += wi * Gzi[c];
-                }
+            if (LAG && (key >> 6) != dA.tile) {
+                a.cross[atomicAdd(&a.cnt->n_cross, 1u)] = r;   // its cell left this tile: k_g2p_cross gathers from the global grid
+            } else {
+                const float4 X = S.rec[stage][0][lane];
+                const int lx = (key >> 4) & 3, ly = (key >> 2) & 3, lz = key & 3;
+                const float fx = __fmul_rn(X.x, a.inv_dx) - (float)(4 * tx + lx);
+                const float fy = __fmul_rn(X.y, a.inv_dx) - (float)(4 * ty + ly);
+                const float fz = __fmul_rn(X.z, a.inv_dx) - (float)(4 * tz + lz);
+                g2p_particle(a, LAG ? r : pA, LAG ? pA : r, X, fx, fy, fz, S.tile + (lx * 36 + ly * 6 + lz), 36, 6, &S.rec[stage][1][lane],
+                             &S.rec[stage][2][lane], &S.rec[stage][3][lane], reinterpret_cast<const int4*>(&S.rec[stage][4][lane]));
             }
-#endif
-            // utils.py:266-275: v, x, C = sum w v (x) (off - f) * 4 inv_dx
-            const float nx = X.x + dt * v[0], ny = X.y + dt * v[1], nz = X.z + dt * v[2];
-            a.oxm[r] = make_float4(nx, ny, nz, X.w);
-            a.ovv[r] = make_float4(v[0], v[1], v[2], 0.f);
-            bool cl = false;
-            const int kx = base_cell(nx, a.inv_dx, n, cl), ky = base_cell(ny, a.inv_dx, n, cl), kz = base_cell(nz, a.inv_dx, n, cl);
-            a.okeys[r] = make_key(kx, ky, kz, a.nt);
-            if (cl) atomicAdd(&a.cnt->n_clamped, 1u);
-            a.oc0[r] = make_float4(Mx[0] * k4, My[0] * k4, Mz[0] * k4, Mx[1] * k4);
-            a.oc1[r] = make_float4(My[1] * k4, Mz[1] * k4, Mx[2] * k4, My[2] * k4);
-            const float C22 = Mz[2] * k4;
-            // grad v = sum v (x) dweight  (row = velocity component, column = derivative direction)
-            float gv[9];
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                gv[3 * c + 0] = Gx[c] * a.inv_dx;
-                gv[3 * c + 1] = Gy[c] * a.inv_dx;
-                gv[3 * c + 2] = Gz[c] * a.inv_dx;
-            }
-            // F_trial = (I + dt grad v) F   (utils.py:276-279)
-            const float4 F0 = S.rec[stage][1][lane], F1 = S.rec[stage][2][lane], F2 = S.rec[stage][3][lane];
-            const float Fo[9] = {F0.x, F0.y, F0.z, F0.w, F1.x, F1.y, F1.z, F1.w, F2.x};
-            float Ft[9];
-#pragma unroll
-            for (int rr = 0; rr < 3; ++rr)
-#pragma unroll
-                for (int c = 0; c < 3; ++c) {
-                    float s = (rr == 0 ? 1.0f + dt * gv[0] : dt * gv[3 * rr + 0]) * Fo[c];
-                    s += (rr == 1 ? 1.0f + dt * gv[4] : dt * gv[3 * rr + 1]) * Fo[3 + c];
-                    s += (rr == 2 ? 1.0f + dt * gv[8] : dt * gv[3 * rr + 2]) * Fo[6 + c];
-                    Ft[3 * rr + c] = s;
-                }
-            if (a.cp.flags & MPMK_WRITE_FTRIAL) {
-                a.ft0[r] = make_float4(Ft[0], Ft[1], Ft[2], Ft[3]);
-                a.ft1[r] = make_float4(Ft[4], Ft[5], Ft[6], Ft[7]);
-                a.ft2[r] = make_float4(Ft[8], F2.w, 0.f, 0.f);   // F2.w: the yield stress before this substep's return map
-            }
-            if (a.cp.flags & MPMK_TRACK_COV) {
-                // update_cov, utils.py:187-215: cov += dt (grad_v cov + cov grad_v^T)
-                const float4 q0 = ldg4(a.cv0 + pA), q1 = ldg4(a.cv1 + pA);
-                const float cn[9] = {q0.x, q0.y, q0.z, q0.y, q0.w, q1.x, q0.z, q1.x, q1.y};
-                float o[9];
-#pragma unroll
-                for (int rr = 0; rr < 3; ++rr)
-#pragma unroll
-                    for (int c = 0; c < 3; ++c) {
-                        float s1 = gv[3 * rr] * cn[c] + gv[3 * rr + 1] * cn[3 + c] + gv[3 * rr + 2] * cn[6 + c];
-                        float s2 = cn[3 * rr] * gv[3 * c] + cn[3 * rr + 1] * gv[3 * c + 1] + cn[3 * rr + 2] * gv[3 * c + 2];
-                        o[3 * rr + c] = cn[3 * rr + c] + dt * (s1 + s2);
-                    }
-                a.ocv0[r] = make_float4(o[0], o[1], o[2], o[4]);
-                a.ocv1[r] = make_float4(o[5], o[8], 0.f, 0.f);
-            }
-            const int4 meta = *reinterpret_cast<const int4*>(&S.rec[stage][4][lane]);
-            a.ometa[r] = meta;
-            // constitutive update for the next substep
-            float mu = F2.y, lam = F2.z, ys = F2.w;
-            float Fn[9], s6[6];
-            constitutive_update(Ft, meta.y, mu, lam, ys, dt, a.cp, Fn, s6);
-            const float vol = __int_as_float(meta.z);
-            a.ocs[r] = make_float4(C22, s6[0], s6[1], s6[2]);
-            a.os1[r] = make_float4(s6[3], s6[4], s6[5], vol);
-            a.of0[r] = make_float4(Fn[0], Fn[1], Fn[2], Fn[3]);
-            a.of1[r] = make_float4(Fn[4], Fn[5], Fn[6], Fn[7]);
-            a.of2[r] = make_float4(Fn[8], mu, lam, ys);
         }
         __syncwarp();  // all lanes are done with the tile and this stage before either is overwritten
         dA = dB; pA = pB;
@@ -274,6 +293,26 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
         kslot = (kslot + 1) % 3;
     }
     cp_async_wait<0>();
+}
+
+// lagged batches: the particles k_g2p<true> deferred, one per thread, stencil nodes straight from the global grid
+__global__ void __launch_bounds__(128) k_g2p_cross(const G2PArgs a) {
+    const uint32_t nc = a.cnt->n_cross;
+    const int n = a.n_grid;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nc; i += gridDim.x * blockDim.x) {
+        const uint32_t r = a.cross[i];
+        const uint32_t key = a.skeys[r];
+        const uint32_t tt = key >> 6;
+        const int bx = 4 * (int)(tt / (uint32_t)(a.nt * a.nt)) + (int)((key >> 4) & 3);
+        const int by = 4 * (int)((tt / (uint32_t)a.nt) % (uint32_t)a.nt) + (int)((key >> 2) & 3);
+        const int bz = 4 * (int)(tt % (uint32_t)a.nt) + (int)(key & 3);
+        const float4 X = a.xm[r];
+        const float fx = __fmul_rn(X.x, a.inv_dx) - (float)bx;
+        const float fy = __fmul_rn(X.y, a.inv_dx) - (float)by;
+        const float fz = __fmul_rn(X.z, a.inv_dx) - (float)bz;
+        g2p_particle(a, r, a.perm[r], X, fx, fy, fz, a.grid_out + (((size_t)bx * n + by) * n + bz), n * n, n, a.f0 + r, a.f1 + r, a.f2 + r,
+                     a.meta + r);
+    }
 }
 
 // utils.py:14-54 on the current set in place (init, and after from_torch edits of F)
@@ -313,22 +352,24 @@ static ConstParams make_cp(const mpmk_ctx* ctx) {
 
 int mpmk_g2p_init(mpmk_ctx* ctx) {
     const int smem = (int)sizeof(G2PWarpSmem) * G2P_WARPS;
-    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_g2p, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_g2p, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_g2p<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_g2p<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_g2p<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_g2p<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     int per_sm = 0;
-    MPMK_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_g2p, G2P_WARPS * 32, smem));
+    MPMK_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_g2p<false>, G2P_WARPS * 32, smem));
     ctx->g2p_ctas_per_sm = per_sm > 0 ? per_sm : 1;
     return 0;
 }
 
-int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s) {
-    if (!ctx->prepared) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_g2p: sort + prepare_grid first");
+static int launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s, bool lag) {
     const int src = ctx->cur, dst = 1 - ctx->cur;
+    uint32_t* keys_out = lag ? (ctx->keys_cur == (uint32_t*)ctx->b.keys ? ctx->keys_b : (uint32_t*)ctx->b.keys) : (uint32_t*)ctx->b.keys;
     if (ctx->n > 0) {
         const mpmk_particle_set& A = ctx->b.set[src];
         const mpmk_particle_set& B = ctx->b.set[dst];
         G2PArgs a;
-        a.perm = ctx->perm; a.skeys = ctx->sorted_keys;
+        a.perm = lag ? ctx->rank : ctx->perm; a.skeys = lag ? ctx->keys_cur : ctx->sorted_keys;
         a.xm = (const float4*)A.xm; a.f0 = (const float4*)A.f0; a.f1 = (const float4*)A.f1; a.f2 = (const float4*)A.f2;
         a.cv0 = (const float4*)A.cv0; a.cv1 = (const float4*)A.cv1; a.meta = (const int4*)A.meta;
         a.oxm = (float4*)B.xm; a.ovv = (float4*)B.vv; a.oc0 = (float4*)B.c0; a.oc1 = (float4*)B.c1; a.ocs = (float4*)B.cs;
@@ -336,7 +377,8 @@ int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s) {
         a.ocv0 = (float4*)B.cv0; a.ocv1 = (float4*)B.cv1; a.ometa = (int4*)B.meta;
         a.ft0 = (float4*)ctx->b.ft0; a.ft1 = (float4*)ctx->b.ft1; a.ft2 = (float4*)ctx->b.ft2;
         a.items = ctx->items;
-        a.okeys = (uint32_t*)ctx->b.keys; a.grid_out = (const float4*)ctx->b.grid_out; a.cnt = ctx->counters;
+        a.okeys = keys_out; a.grid_out = (const float4*)ctx->b.grid_out; a.cnt = ctx->counters;
+        a.cross = ctx->cross_list;
         a.n = ctx->n; a.n_grid = ctx->n_grid; a.nt = ctx->nt; a.inv_dx = ctx->inv_dx; a.dt = dt;
         a.cp = make_cp(ctx);
         if ((a.cp.flags & MPMK_TRACK_COV) && (!A.cv0 || !A.cv1 || !B.cv0 || !B.cv1))
@@ -346,16 +388,32 @@ int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s) {
         // persistent grid, warps fetch work items dynamically (counters->g2p_cursor, zeroed by prepare)
         int64_t want = (ctx->n / 32 + G2P_WARPS - 1) / G2P_WARPS + 1;
         int64_t cap = (int64_t)ctx->sm_count * ctx->g2p_ctas_per_sm;
-        mpmk_launch(k_g2p, dim3((int)(want < cap ? want : cap)), dim3(G2P_WARPS * 32), sizeof(G2PWarpSmem) * G2P_WARPS, s, a);
+        const dim3 grid((int)(want < cap ? want : cap));
+        if (lag) {
+            mpmk_launch(k_g2p<true>, grid, dim3(G2P_WARPS * 32), sizeof(G2PWarpSmem) * G2P_WARPS, s, a);
+            MPMK_LAUNCH_CHECK(ctx);
+            k_g2p_cross<<<ctx->sm_count, 128, 0, s>>>(a);
+        } else {
+            mpmk_launch(k_g2p<false>, grid, dim3(G2P_WARPS * 32), sizeof(G2PWarpSmem) * G2P_WARPS, s, a);
+        }
         MPMK_LAUNCH_CHECK(ctx);
     }
     ctx->cur = dst;
+    if (lag) ctx->keys_cur = keys_out;
     ctx->ftrial_valid = (ctx->prm.flags & MPMK_WRITE_FTRIAL) != 0;
     ctx->sorted_valid = false;  // the permutation referred to the old physical order
     ctx->coherent = true;       // ... but sorted_keys[r] is now the old key of physical slot r (sort.cu, coherent sort)
     ctx->prepared = false;
     return 0;
 }
+
+int mpmk_launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s) {
+    if (!ctx->prepared) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_g2p: sort + prepare_grid first");
+    ctx->lag_ready = false;
+    return launch_g2p(ctx, dt, s, false);
+}
+
+int mpmk_launch_g2p_lagged(mpmk_ctx* ctx, float dt, cudaStream_t s) { return launch_g2p(ctx, dt, s, true); }
 
 extern "C" int mpmk_constitutive_ex(mpmk_ctx* ctx, float dt, int use_ftrial, int use_ys_before, void* stream) {
     if (!ctx || !ctx->bound) return MPMK_ERR_STATE;

@@ -84,8 +84,7 @@ __global__ void __launch_bounds__(256) k_grid_planes(float4* __restrict__ gin, f
     }
 }
 
-int mpmk_launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s) {
-    if (!ctx->prepared) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_grid_update: prepare_grid first");
+static int launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s, bool zero_in) {
     GridOpsArg a;
     a.n_ops = 0;
     if (ops) {
@@ -96,7 +95,7 @@ int mpmk_launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaS
     mpmk_launch(k_grid, dim3(ctx->sm_count * 8), dim3(256), 0, s, (float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out,
                                              ctx->block_list[ctx->cur_list], ctx->block_count[ctx->cur_list],
                                              ctx->n_grid, ctx->nb, ctx->dx, dt, ctx->prm.gravity[0], ctx->prm.gravity[1],
-                                             ctx->prm.gravity[2], a, ctx->zero_grid_in ? 1 : 0);
+                                             ctx->prm.gravity[2], a, (zero_in || ctx->zero_grid_in) ? 1 : 0);
     MPMK_LAUNCH_CHECK(ctx);
     if (ctx->mg.enabled) {
         const MgState& m = ctx->mg;
@@ -111,3 +110,11 @@ int mpmk_launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaS
     }
     return 0;
 }
+
+int mpmk_launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s) {
+    if (!ctx->prepared) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_grid_update: prepare_grid first");
+    return launch_grid(ctx, dt, ops, s, false);
+}
+
+// lagged batches: no `prepared` state to check (the lists were built a substep ago)
+int mpmk_launch_grid_lagged(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s) { return launch_grid(ctx, dt, ops, s, false); }

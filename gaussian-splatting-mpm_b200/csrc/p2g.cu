@@ -10,12 +10,19 @@
 //     (R_k is stored divided by the particle mass and Y_ij carries m wx_i wy_j in its 4th lane);
 //   phase B (lane = stencil node (i,j,k)): walks the batch in sorted order; node value
 //         wz_k Y_ij + (m wx_i wy_j) R_k / m,  mass (m wx_i wy_j) wz_k
-//     accumulates in registers while consecutive particles share a cell -- the runs are the groups
-//     __match_any_sync finds in phase A, their heads collected with one ballot per batch -- and is
+//     accumulates in registers while consecutive particles share a cell -- run heads are the lanes whose cell
+//     differs from their predecessor's, collected with one ballot per batch -- and is
 //     added to the shared tile once per (cell run, node): no shared-memory atomics, every lane owns a
 //     distinct node.
 // The tile is flushed with one 16-byte red.global.add.v4.f32 per non-zero node.
+//
+// LAG = true (lagged batches, api.cu): the work list was built from the sort of the PREVIOUS substep and the physical
+// order is that sorted order, so a batch is 32 consecutive physical slots (no permutation) and a particle's cell
+// comes from its current key.  A particle that changed cell inside the item's tile simply starts a run of its own; one
+// whose cell left the tile ("crosser", ~1 % per substep) is accumulated the same way and its 27 node values go straight
+// to the global grid, with the node blocks they touch added to this substep's block list.
 #include "common.cuh"
+#include <cstdlib>
 
 #ifndef P2G_WARPS
 #define P2G_WARPS 4
@@ -42,9 +49,16 @@ struct __align__(16) P2GWarpSmem {
     float4 stage[P2G_NSTAGE][32];  // next batch's particle records, in flight (cp.async) while this batch is scattered
 };
 
+#define P2G_CROSS 0x40000000   // cell code of a crosser: P2G_CROSS | bx | by << 10 | bz << 20 (base cell, n_grid <= 1023)
+
 struct P2GArgs {
-    const uint32_t* perm;
-    const uint32_t* skeys;
+    const uint32_t* perm;    // LAG: unused
+    const uint32_t* skeys;   // LAG: the current keys, in physical order
+    // LAG: this substep's block list, for the blocks only crossers reach
+    uint32_t* stamp_arr;
+    uint32_t* blist;
+    uint32_t* bcount;
+    int nb;
     const float4 *xm, *vv, *c0, *c1, *cs, *s1;
     const uint4* items;
     DevCounters* cnt;
@@ -55,6 +69,26 @@ struct P2GArgs {
     mpmk_impulse imp[MPMK_MAX_IMPULSES];
 };
 
+// one cell run's accumulated node value -> the warp's tile, or (crossers) the global grid
+template <bool LAG>
+__device__ __forceinline__ void p2g_flush_run(const P2GArgs& a, float4* tile, int cur_cell, int noff, int ni, int nj, int nk,
+                                              const float4& acc, const float4& acc2, uint32_t stamp) {
+    const float4 v = make_float4(acc.x + acc2.x, acc.y + acc2.y, acc.z + acc2.z, acc.w);
+    if (!LAG || cur_cell < 64) {
+        const int nd = (cur_cell >> 4) * P2G_TILE_SX + ((cur_cell >> 2) & 3) * 6 + (cur_cell & 3) + noff;
+        float4 t = tile[nd];
+        t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
+        tile[nd] = t;
+    } else {
+        const int gx = (cur_cell & 1023) + ni, gy = ((cur_cell >> 10) & 1023) + nj, gz = ((cur_cell >> 20) & 1023) + nk;
+        const int n = a.n_grid;
+        red_add_v4(a.grid_in + (((size_t)gx * n + gy) * n + gz), v);
+        const uint32_t b = (uint32_t)(((gx >> 2) * a.nb + (gy >> 2)) * a.nb + (gz >> 2));
+        if (atomicExch(&a.stamp_arr[b], stamp) != stamp) a.blist[atomicAdd(a.bcount, 1u)] = b;
+    }
+}
+
+template <bool LAG>
 __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GArgs a) {
     pdl_wait();   // programmatic dependent launch: nothing of the previous grid is read or overwritten before this
     extern __shared__ float4 smem_raw[];
@@ -77,12 +111,13 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
     BatchStream bs;
     bs.init();
     const uint32_t n_items = a.cnt->n_items;
+    const uint32_t stamp = LAG ? a.cnt->list_stamp : 0u;
     BatchDesc dA = bs.next(lane, a.items, &a.cnt->p2g_cursor, n_items);
     if (dA.count == 0) return;
     uint32_t pA = 0, kA = 0, pB = 0, kB = 0, pC = 0, kC = 0;
-    if (lane < dA.count) { pA = a.perm[dA.base + lane]; kA = a.skeys[dA.base + lane]; }
+    if (lane < dA.count) { pA = LAG ? dA.base + lane : a.perm[dA.base + lane]; kA = a.skeys[dA.base + lane]; }
     BatchDesc dB = bs.next(lane, a.items, &a.cnt->p2g_cursor, n_items);
-    if (lane < dB.count) { pB = a.perm[dB.base + lane]; kB = a.skeys[dB.base + lane]; }
+    if (lane < dB.count) { pB = LAG ? dB.base + lane : a.perm[dB.base + lane]; kB = a.skeys[dB.base + lane]; }
     if (lane < dA.count) {
         cp_async16(&S.stage[0][lane], a.xm + pA); cp_async16(&S.stage[1][lane], a.vv + pA);
         cp_async16(&S.stage[2][lane], a.c0 + pA); cp_async16(&S.stage[3][lane], a.c1 + pA);
@@ -111,12 +146,19 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
             }
             cp_async_commit();
             const BatchDesc dC = bs.next(lane, a.items, &a.cnt->p2g_cursor, n_items);
-            if (lane < dC.count) { pC = a.perm[dC.base + lane]; kC = a.skeys[dC.base + lane]; }
+            if (lane < dC.count) { pC = LAG ? dC.base + lane : a.perm[dC.base + lane]; kC = a.skeys[dC.base + lane]; }
             // ---------------- phase A: lane = particle ----------------
             if (lane < nbatch) {
                 const uint32_t key = kA;
                 my_cell = key & 63;
-                const int lx = my_cell >> 4, ly = (my_cell >> 2) & 3, lz = my_cell & 3;
+                int bx = 4 * tx + (my_cell >> 4), by = 4 * ty + ((my_cell >> 2) & 3), bz = 4 * tz + (my_cell & 3);   // base cell
+                if (LAG && (key >> 6) != dA.tile) {   // the particle's cell left this item's tile since the list was built
+                    const uint32_t tt = key >> 6;
+                    bx = 4 * (int)(tt / (uint32_t)(a.nt * a.nt)) + (my_cell >> 4);
+                    by = 4 * (int)((tt / (uint32_t)a.nt) % (uint32_t)a.nt) + ((my_cell >> 2) & 3);
+                    bz = 4 * (int)(tt % (uint32_t)a.nt) + (my_cell & 3);
+                    my_cell = P2G_CROSS | bx | (by << 10) | (bz << 20);
+                }
                 const float m = X.w, vol = S1.w;
                 const float inv_m = m > 0.f ? __frcp_rn(m) : 0.f;
                 float vx = V.x, vy = V.y, vz = V.z;
@@ -129,9 +171,9 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
                         vz = vz + __fdiv_rn(im.force[2], m) * im.substep_dt;
                     }
                 }
-                const float fx = __fmul_rn(X.x, a.inv_dx) - (float)(4 * tx + lx);
-                const float fy = __fmul_rn(X.y, a.inv_dx) - (float)(4 * ty + ly);
-                const float fz = __fmul_rn(X.z, a.inv_dx) - (float)(4 * tz + lz);
+                const float fx = __fmul_rn(X.x, a.inv_dx) - (float)bx;
+                const float fy = __fmul_rn(X.y, a.inv_dx) - (float)by;
+                const float fz = __fmul_rn(X.z, a.inv_dx) - (float)bz;
                 float wx[3], wy[3], wz[3], dwx[3], dwy[3], dwz[3];
                 {
                     float wa = 1.5f - fx, wb = fx - 1.0f, wc = fx - 0.5f;
@@ -191,23 +233,18 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
             }
             __syncwarp();
             // ---------------- phase B: lane = stencil node ----------------
-            // run heads: the lowest lane of each __match_any_sync group (lane 0 continues the run carried
-            // over from the previous batch when the cell is the same)
-            // (sorted input: the lanes sharing a cell are contiguous, so a run's head is its lowest peer)
-            const unsigned peers = __match_any_sync(0xffffffffu, my_cell);
-            const bool head = (lane < nbatch) && (lane == __ffs(peers) - 1) && !(lane == 0 && my_cell == cur_cell);
+            // run heads: lanes whose cell differs from the lane before them (lane 0: from the run carried over from
+            // the previous batch).  Sorted input makes a cell's particles contiguous; in a lagged batch a particle that
+            // changed cell sits inside its old cell's run and splits it.
+            const int prev_cell = __shfl_up_sync(0xffffffffu, my_cell, 1);
+            const bool head = (lane < nbatch) && (my_cell != (lane == 0 ? cur_cell : prev_cell));
             const unsigned heads = __ballot_sync(0xffffffffu, head);
             const float4* recY = S.rec + nij * P2G_REC_STRIDE;
             const float4* recR = S.rec + (9 + nk) * P2G_REC_STRIDE;
             int l = 0;
             while (l < nbatch) {
                 if ((heads >> l) & 1u) {
-                    if (cur_cell >= 0 && node_lane) {
-                        const int nd = (cur_cell >> 4) * P2G_TILE_SX + ((cur_cell >> 2) & 3) * 6 + (cur_cell & 3) + noff;
-                        float4 t = S.tile[nd];
-                        t.x += acc.x + acc2.x; t.y += acc.y + acc2.y; t.z += acc.z + acc2.z; t.w += acc.w;
-                        S.tile[nd] = t;
-                    }
+                    if (cur_cell >= 0 && node_lane) p2g_flush_run<LAG>(a, S.tile, cur_cell, noff, ni, nj, nk, acc, acc2, stamp);
                     acc = zero4; acc2 = zero4;
                     cur_cell = __shfl_sync(0xffffffffu, my_cell, l);
                 }
@@ -228,12 +265,7 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
             __syncwarp();
             // end of the item: last cell run -> tile, tile -> global grid (16-byte vector reductions)
             if (dB.count == 0 || dB.first) {
-                if (cur_cell >= 0 && node_lane) {
-                    const int nd = (cur_cell >> 4) * P2G_TILE_SX + ((cur_cell >> 2) & 3) * 6 + (cur_cell & 3) + noff;
-                    float4 t = S.tile[nd];
-                    t.x += acc.x + acc2.x; t.y += acc.y + acc2.y; t.z += acc.z + acc2.z; t.w += acc.w;
-                    S.tile[nd] = t;
-                }
+                if (cur_cell >= 0 && node_lane) p2g_flush_run<LAG>(a, S.tile, cur_cell, noff, ni, nj, nk, acc, acc2, stamp);
                 __syncwarp();
                 for (int i = lane; i < MPMK_TILE_NODES; i += 32) {
                     const int ti = i + i / 36;  // x*37 + y*6 + z
@@ -253,12 +285,13 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
     }
 }
 
-int mpmk_launch_p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s) {
-    if (!ctx->prepared) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_p2g: prepare_grid first");
+static int launch_p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s, bool lag) {
     if (ctx->n == 0) return 0;
     const mpmk_particle_set& ps = ctx->b.set[ctx->cur];
     P2GArgs a;
-    a.perm = ctx->perm; a.skeys = ctx->sorted_keys;
+    a.perm = ctx->perm; a.skeys = lag ? ctx->keys_cur : ctx->sorted_keys;
+    a.stamp_arr = ctx->block_stamp[ctx->cur_list]; a.blist = ctx->block_list[ctx->cur_list]; a.bcount = ctx->block_count[ctx->cur_list];
+    a.nb = ctx->nb;
     a.xm = (const float4*)ps.xm; a.vv = (const float4*)ps.vv; a.c0 = (const float4*)ps.c0;
     a.c1 = (const float4*)ps.c1; a.cs = (const float4*)ps.cs; a.s1 = (const float4*)ps.s1;
     a.items = ctx->items; a.cnt = ctx->counters; a.grid_in = (float4*)ctx->b.grid_in;
@@ -272,19 +305,34 @@ int mpmk_launch_p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaSt
     const int smem = (int)sizeof(P2GWarpSmem) * P2G_WARPS;
     // persistent grid: as many CTAs as fit per SM, warps fetch items dynamically
     int64_t want = (ctx->n / 32 + P2G_WARPS - 1) / P2G_WARPS + 1;
-    int64_t cap = (int64_t)ctx->sm_count * ctx->p2g_ctas_per_sm;
+    int64_t cap = (int64_t)ctx->sm_count * (lag ? ctx->p2g_lag_ctas_per_sm : ctx->p2g_ctas_per_sm);
     int grid = (int)(want < cap ? want : cap);
-    mpmk_launch(k_p2g, dim3(grid), dim3(P2G_WARPS * 32), smem, s, a);
+    if (lag) mpmk_launch(k_p2g<true>, dim3(grid), dim3(P2G_WARPS * 32), smem, s, a);
+    else mpmk_launch(k_p2g<false>, dim3(grid), dim3(P2G_WARPS * 32), smem, s, a);
     MPMK_LAUNCH_CHECK(ctx);
     return 0;
 }
 
+int mpmk_launch_p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s) {
+    if (!ctx->prepared) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_p2g: prepare_grid first");
+    return launch_p2g(ctx, dt, ops, s, false);
+}
+
+int mpmk_launch_p2g_lagged(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s) { return launch_p2g(ctx, dt, ops, s, true); }
+
 int mpmk_p2g_init(mpmk_ctx* ctx) {
     const int smem = (int)sizeof(P2GWarpSmem) * P2G_WARPS;
-    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_p2g, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_p2g, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_p2g<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_p2g<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_p2g<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_p2g<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     int per_sm = 0;
-    MPMK_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_p2g, P2G_WARPS * 32, smem));
+    MPMK_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_p2g<false>, P2G_WARPS * 32, smem));
     ctx->p2g_ctas_per_sm = per_sm > 0 ? per_sm : 1;
+    MPMK_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_p2g<true>, P2G_WARPS * 32, smem));
+    ctx->p2g_lag_ctas_per_sm = per_sm > 0 ? per_sm : 1;
+    // the side branch (sort + work lists of the next substep) needs room beside the persistent scatter grid
+    static const int leave = getenv("MPMK_LAG_P2G_CTAS") ? atoi(getenv("MPMK_LAG_P2G_CTAS")) : 0;
+    if (leave > 0 && leave < ctx->p2g_lag_ctas_per_sm) ctx->p2g_lag_ctas_per_sm = leave;
     return 0;
 }

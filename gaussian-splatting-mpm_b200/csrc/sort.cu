@@ -21,6 +21,7 @@ int mpmk_launch_keys(mpmk_ctx* ctx, cudaStream_t s) {
     k_keys<<<div_up(ctx->n, 256), 256, 0, s>>>((const float4*)ctx->b.set[ctx->cur].xm, (uint32_t*)ctx->b.keys, ctx->n,
                                                ctx->inv_dx, ctx->n_grid, ctx->nt, ctx->counters);
     MPMK_LAUNCH_CHECK(ctx);
+    ctx->lag_ready = false;
     ctx->sorted_valid = false;
     ctx->coherent = false;   // the host rewrote positions: the old sorted keys say nothing about the new ones
     ctx->prepared = false;
@@ -488,7 +489,8 @@ __global__ void __launch_bounds__(256) k_cs_place_movers(const uint32_t* __restr
                                                          int64_t n, const uint32_t* __restrict__ mask,
                                                          const uint32_t* __restrict__ mprefix, uint32_t* __restrict__ cnt,
                                                          uint32_t* __restrict__ mx, uint32_t* __restrict__ out_keys,
-                                                         uint32_t* __restrict__ out_perm, const uint32_t* __restrict__ samples) {
+                                                         uint32_t* __restrict__ out_perm, const uint32_t* __restrict__ samples,
+                                                         uint32_t* __restrict__ rank) {
     pdl_wait();   // programmatic dependent launch: nothing of the previous grid is read or overwritten before this
     const uint32_t M = ctrl[CS_CTRL_MOVERS];
     const uint32_t N = (uint32_t)n;
@@ -538,6 +540,7 @@ __global__ void __launch_bounds__(256) k_cs_place_movers(const uint32_t* __restr
         const uint32_t pos = t + (x - movers_before);
         out_keys[pos] = kj;
         out_perm[pos] = j;
+        if (rank) rank[j] = pos;   // lagged batches: g2p writes slot j's particle to sorted position pos
         mx[t] = x;
         if (x < N) atomicAdd(&cnt[x >> 5], 1u);
     }
@@ -548,7 +551,8 @@ __global__ void __launch_bounds__(CS_THREADS) k_cs_place_stayers(const uint32_t*
                                                                  const uint32_t* __restrict__ mask,
                                                                  const uint32_t* __restrict__ mprefix,
                                                                  const uint32_t* __restrict__ cnt, const uint32_t* __restrict__ mx,
-                                                                 uint32_t* __restrict__ out_keys, uint32_t* __restrict__ out_perm) {
+                                                                 uint32_t* __restrict__ out_keys, uint32_t* __restrict__ out_perm,
+                                                                 uint32_t* __restrict__ rank) {
     pdl_wait();   // programmatic dependent launch: nothing of the previous grid is read or overwritten before this
     __shared__ uint32_t chunk_s, excl_s;
     __shared__ uint32_t wsum[CS_THREADS / 32];
@@ -589,13 +593,19 @@ __global__ void __launch_bounds__(CS_THREADS) k_cs_place_stayers(const uint32_t*
             const uint32_t pos = ((uint32_t)slot - (mp + __popc(m & lt))) + c;
             out_keys[pos] = k[r];
             out_perm[pos] = (uint32_t)slot;
+            if (rank) rank[slot] = pos;
         }
     }
     }   // next chunk
 }
 
+// inverse of the permutation (full radix path of a lagged batch; the merge path writes the ranks as it places)
+__global__ void __launch_bounds__(256) k_invert_perm(const uint32_t* __restrict__ perm, uint32_t* __restrict__ rank, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) rank[perm[i]] = (uint32_t)i;
+}
+
 template <int BITS>
-static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s) {
+static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s, bool want_rank) {
     constexpr int D = 1 << BITS;
     const int ntiles = div_up(ctx->n, MPMK_SORT_CHUNK);   // == chunks of the scans (CS_CHUNK == MPMK_SORT_CHUNK)
     static_assert(CS_CHUNK == MPMK_SORT_CHUNK, "the scans and the radix tiles share the control block sizing");
@@ -606,7 +616,8 @@ static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     uint32_t* status_a = ctrl + OS_CTRL_STATUS + radix_status;
     uint32_t* status_b = status_a + ntiles;
     const uint32_t* okeys = ctx->sorted_keys;
-    const uint32_t* keys = (const uint32_t*)ctx->b.keys;
+    const uint32_t* keys = ctx->keys_cur;
+    uint32_t* rank = want_rank ? ctx->rank : nullptr;
     const int first = passes & 1;   // the compacted movers start in this buffer so that the last radix pass lands in buffer 0
     mpmk_launch(k_cs_flag_scan, dim3(min(ntiles, ctx->sm_count * 5)), dim3(CS_THREADS), 0, s, keys, okeys, ctx->n, ctrl, status_a, ctx->cs_mask, ctx->cs_mprefix, ctx->cs_cnt,
                                                  ctx->cs_mk[first], ctx->cs_mv[first], BITS, passes, ctx->hist_tot);   // hist_tot: 1024 key samples
@@ -626,10 +637,10 @@ static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     // sorted movers are in buffer `in` (== 0); the other key buffer is free and receives x_t
     uint32_t* mx = ctx->cs_mk[1 - in];
     mpmk_launch(k_cs_place_movers, dim3(ctx->sm_count * 4), dim3(256), 0, s, ctx->cs_mk[in], ctx->cs_mv[in], ctrl, okeys, ctx->n, ctx->cs_mask, ctx->cs_mprefix,
-                                                        ctx->cs_cnt, mx, ctx->keys_alt, ctx->perm, ctx->hist_tot);
+                                                        ctx->cs_cnt, mx, ctx->keys_alt, ctx->perm, ctx->hist_tot, rank);
     MPMK_LAUNCH_CHECK(ctx);
     mpmk_launch(k_cs_place_stayers, dim3(min(ntiles, ctx->sm_count * 4)), dim3(CS_THREADS), 0, s, keys, ctx->n, ctrl, status_b, ctx->cs_mask, ctx->cs_mprefix, ctx->cs_cnt, mx,
-                                                     ctx->keys_alt, ctx->perm);
+                                                     ctx->keys_alt, ctx->perm, rank);
     MPMK_LAUNCH_CHECK(ctx);
     uint32_t* t = ctx->sorted_keys; ctx->sorted_keys = ctx->keys_alt; ctx->keys_alt = t;
     ctx->last_sort_coherent = true;
@@ -637,13 +648,13 @@ static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s) {
 }
 
 template <int BITS>
-static int sort_all(mpmk_ctx* ctx, int passes, cudaStream_t s) {
+static int sort_all(mpmk_ctx* ctx, int passes, cudaStream_t s, bool want_rank) {
     constexpr int D = 1 << BITS;
     const int ntiles = div_up(ctx->n, MPMK_SORT_CHUNK);
     // below ~1.5 M particles the full sort's three or four kernels are quicker than the merge's six (measured on the
     // config-shaped scenes: 240 k particles 37 vs 47 us, 1 M 57 vs 65 us, 3.6 M 87 vs 68 us); MPMK_SORT_MERGE forces it
     if (ctx->coherent && !(ctx->prm.flags & MPMK_SORT_FULL) && (ctx->n >= MPMK_COHERENT_MIN_N || (ctx->prm.flags & MPMK_SORT_MERGE)))
-        return sort_coherent<BITS>(ctx, passes, s);
+        return sort_coherent<BITS>(ctx, passes, s, want_rank);
     ctx->last_sort_coherent = false;
     // small clouds re-sort in full every substep, and there a pass costs the latency of ONE tile (a warp's serial
     // instruction stream: ranking rounds, re-staging, write-out), not throughput: twice the threads, half the rounds
@@ -653,11 +664,11 @@ static int sort_all(mpmk_ctx* ctx, int passes, cudaStream_t s) {
     const size_t ctrl_words = OS_CTRL_STATUS + (size_t)passes * otiles * D;
     MPMK_CHECK(ctx, cudaMemsetAsync(ctx->sort_ctrl, 0, ctrl_words * 4, s));
     int hgrid = ntiles < ctx->sm_count * 4 ? ntiles : ctx->sm_count * 4;
-    mpmk_launch(k_sort_digit_hist<BITS>, dim3(hgrid), dim3(256), 0, s, (const uint32_t*)ctx->b.keys, ctx->n, nullptr, passes, ctx->sort_ctrl);
+    mpmk_launch(k_sort_digit_hist<BITS>, dim3(hgrid), dim3(256), 0, s, (const uint32_t*)ctx->keys_cur, ctx->n, nullptr, passes, ctx->sort_ctrl);
     MPMK_LAUNCH_CHECK(ctx);
     uint32_t* kb[2] = {ctx->sorted_keys, ctx->keys_alt};
     uint32_t* vb[2] = {ctx->perm, ctx->perm_alt};
-    const uint32_t* kin = (const uint32_t*)ctx->b.keys;
+    const uint32_t* kin = (const uint32_t*)ctx->keys_cur;
     const uint32_t* vin = nullptr;
     constexpr int stage_bytes = 2 * MPMK_SORT_CHUNK * 4 + (256 / 32) * D * 4;
     constexpr int stage_bytes_small = 2 * MPMK_SORT_CHUNK * 4 + (512 / 32) * D * 4;
@@ -675,6 +686,10 @@ static int sort_all(mpmk_ctx* ctx, int passes, cudaStream_t s) {
         kin = kb[o];
         vin = vb[o];
     }
+    if (want_rank) {
+        k_invert_perm<<<min(div_up(ctx->n, 256), ctx->sm_count * 8), 256, 0, s>>>(ctx->perm, ctx->rank, ctx->n);
+        MPMK_LAUNCH_CHECK(ctx);
+    }
     return 0;
 }
 
@@ -686,6 +701,11 @@ static int sort_init_bits(mpmk_ctx* ctx) {
                                          2 * MPMK_SORT_CHUNK * 4 + (256 / 32) * D * 4));
     MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 512, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          2 * MPMK_SORT_CHUNK * 4 + (512 / 32) * D * 4));
+    // lagged batches run the sort beside the persistent p2g grid: an SM only hosts kernels of one shared-memory
+    // configuration at a time, so everything on the side branch asks for the same (maximal) carve-out as p2g
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 256, 16>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 512, 8>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_digit_hist<BITS>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     return 0;
 }
 
@@ -694,21 +714,30 @@ int mpmk_sort_init(mpmk_ctx* ctx) {
     if ((rc = sort_init_bits<5>(ctx)) || (rc = sort_init_bits<6>(ctx)) || (rc = sort_init_bits<7>(ctx)) ||
         (rc = sort_init_bits<8>(ctx)) || (rc = sort_init_bits<9>(ctx)))
         return rc;
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_cs_flag_scan, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_cs_place_movers, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_cs_place_stayers, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_invert_perm, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     return 0;
 }
 
-int mpmk_launch_sort(mpmk_ctx* ctx, cudaStream_t s) {
+static int launch_sort_impl(mpmk_ctx* ctx, cudaStream_t s, bool want_rank);
+int mpmk_launch_sort(mpmk_ctx* ctx, cudaStream_t s) { return launch_sort_impl(ctx, s, false); }
+// lagged batches: the same sort of the current keys (ctx->keys_cur), plus the inverse permutation for g2p's scatter
+int mpmk_launch_sort_lagged(mpmk_ctx* ctx, cudaStream_t s) { return launch_sort_impl(ctx, s, true); }
+
+static int launch_sort_impl(mpmk_ctx* ctx, cudaStream_t s, bool want_rank) {
     if (ctx->n == 0) { ctx->sorted_valid = true; return 0; }
     int passes = (ctx->key_bits + MPMK_MAX_RADIX_BITS - 1) / MPMK_MAX_RADIX_BITS;
     int bits = (ctx->key_bits + passes - 1) / passes;
     if (bits < 5) bits = 5;
     int rc;
     switch (bits) {
-        case 5: rc = sort_all<5>(ctx, passes, s); break;
-        case 6: rc = sort_all<6>(ctx, passes, s); break;
-        case 7: rc = sort_all<7>(ctx, passes, s); break;
-        case 8: rc = sort_all<8>(ctx, passes, s); break;
-        default: rc = sort_all<9>(ctx, passes, s); break;
+        case 5: rc = sort_all<5>(ctx, passes, s, want_rank); break;
+        case 6: rc = sort_all<6>(ctx, passes, s, want_rank); break;
+        case 7: rc = sort_all<7>(ctx, passes, s, want_rank); break;
+        case 8: rc = sort_all<8>(ctx, passes, s, want_rank); break;
+        default: rc = sort_all<9>(ctx, passes, s, want_rank); break;
     }
     if (rc) return rc;
     ctx->sorted_valid = true;

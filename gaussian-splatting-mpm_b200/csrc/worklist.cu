@@ -15,7 +15,7 @@ __global__ void k_clear_blocks(float4* __restrict__ gin, float4* __restrict__ go
         *stamp += 1u;  // consumed by k_build_items (a later launch on the stream)
         // this substep's counters / block list start empty (the previous substep's kernels are done with them)
         cnt->n_items = 0u; cnt->n_active_blocks = 0u; cnt->n_tiles = 0u; cnt->n_clamped = 0u;
-        cnt->p2g_cursor = 0u; cnt->g2p_cursor = 0u;
+        cnt->p2g_cursor = 0u; cnt->g2p_cursor = 0u; cnt->n_cross = 0u; cnt->list_stamp = *stamp;
         *next_count = 0u;
     }
     const int64_t total = (int64_t)(*count) * 64;
@@ -168,33 +168,168 @@ int mpmk_item_size(const mpmk_ctx* ctx) {
     return (int)sz;
 }
 
+// tile runs + work items + block list of the current sort, into work-list set `w` / block list `l` (whose counters
+// and count have been reset, and whose stamp has been advanced, by the kernel that ran before)
+static int launch_build(mpmk_ctx* ctx, int w, int l, cudaStream_t s) {
+    if (ctx->n <= 0) return 0;
+    DevCounters* cnt = ctx->counters_buf[w];
+    mpmk_launch(k_tile_runs, dim3(min(div_up(ctx->n, 4096), ctx->sm_count * 8)), dim3(256), 0, s, ctx->sorted_keys, ctx->n, ctx->tile_list, ctx->tile_end, cnt);
+    MPMK_LAUNCH_CHECK(ctx);
+    // at most nt^3 tiles exist: with few of them a whole warp takes one tile
+    const int64_t tile_bound = min((int64_t)ctx->nt * ctx->nt * ctx->nt, ctx->n);
+    const uint32_t item_max = (uint32_t)mpmk_item_size(ctx);
+    if (tile_bound <= 16384)
+        mpmk_launch(k_build_items<32>, dim3((int)min((int64_t)ctx->sm_count * 8, (int64_t)div_up(tile_bound, 8))), dim3(256), 0, s,
+            ctx->tile_list, ctx->tile_end, ctx->items_buf[w], cnt, ctx->block_stamp[l], ctx->dev_stamp, ctx->block_list[l],
+            ctx->block_count[l], ctx->nt, ctx->nb, item_max);
+    else
+        mpmk_launch(k_build_items<1>, dim3(ctx->sm_count), dim3(256), 0, s, ctx->tile_list, ctx->tile_end, ctx->items_buf[w], cnt, ctx->block_stamp[l],
+                                                       ctx->dev_stamp, ctx->block_list[l], ctx->block_count[l], ctx->nt,
+                                                       ctx->nb, item_max);
+    MPMK_LAUNCH_CHECK(ctx);
+    return 0;
+}
+
+static void use_worklist(mpmk_ctx* ctx, int w) {
+    ctx->wl = w;
+    ctx->items = ctx->items_buf[w];
+    ctx->counters = ctx->counters_buf[w];
+}
+
 int mpmk_launch_prepare(mpmk_ctx* ctx, cudaStream_t s) {
     if (!ctx->sorted_valid) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_prepare_grid: sort first");
     int prev = ctx->cur_list;
     int next = 1 - prev;
+    const int w = 1 - ctx->wl;
     // clear what the previous substep touched; reset the per-substep counters
     mpmk_launch(k_clear_blocks, dim3(ctx->sm_count * 8), dim3(256), 0, s, (float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out,
                                                      ctx->block_list[prev], ctx->block_count[prev], ctx->n_grid, ctx->nb,
-                                                     ctx->dev_stamp, ctx->counters, ctx->block_count[next], ctx->keep_grid_in ? 0 : 1);
+                                                     ctx->dev_stamp, ctx->counters_buf[w], ctx->block_count[next], ctx->keep_grid_in ? 0 : 1);
     MPMK_LAUNCH_CHECK(ctx);
     // (slab mode: the shared planes are reset by k_grid_planes, which visits every node of them each substep)
-    if (ctx->n > 0) {
-        mpmk_launch(k_tile_runs, dim3(min(div_up(ctx->n, 4096), ctx->sm_count * 8)), dim3(256), 0, s, ctx->sorted_keys, ctx->n, ctx->tile_list, ctx->tile_end, ctx->counters);
-        MPMK_LAUNCH_CHECK(ctx);
-        // at most nt^3 tiles exist: with few of them a whole warp takes one tile
-        const int64_t tile_bound = min((int64_t)ctx->nt * ctx->nt * ctx->nt, ctx->n);
-        const uint32_t item_max = (uint32_t)mpmk_item_size(ctx);
-        if (tile_bound <= 16384)
-            mpmk_launch(k_build_items<32>, dim3((int)min((int64_t)ctx->sm_count * 8, (int64_t)div_up(tile_bound, 8))), dim3(256), 0, s, 
-                ctx->tile_list, ctx->tile_end, ctx->items, ctx->counters, ctx->block_stamp, ctx->dev_stamp, ctx->block_list[next],
-                ctx->block_count[next], ctx->nt, ctx->nb, item_max);
-        else
-            mpmk_launch(k_build_items<1>, dim3(ctx->sm_count), dim3(256), 0, s, ctx->tile_list, ctx->tile_end, ctx->items, ctx->counters, ctx->block_stamp,
-                                                           ctx->dev_stamp, ctx->block_list[next], ctx->block_count[next], ctx->nt,
-                                                           ctx->nb, item_max);
-        MPMK_LAUNCH_CHECK(ctx);
-    }
+    { int rc = launch_build(ctx, w, next, s); if (rc) return rc; }
+    use_worklist(ctx, w);
     ctx->cur_list = next;
     ctx->prepared = true;
+    ctx->lag_ready = false;
     return 0;
+}
+
+// ---- lagged batches (api.cu) ----------------------------------------------------------------------
+// From the second substep of a batch on, p2g / grid / g2p of substep s run on the work list and the block list that
+// were built from the sort of substep s-1 (the physical order IS that sorted order; a particle's true cell comes
+// from its current key), while the sort of substep s and the lists for substep s+1 are built on a side branch.
+
+// Clears grid_out over block list [l] (the blocks of the substep before the last: g2p has read them), then -- last
+// CTA out -- resets that list's count and the counters of work-list set [w] for the rebuild that follows on the stream
+// (the same buffers: a separate launch would only be there to order the reset after the clear).
+__global__ void __launch_bounds__(256) k_lag_clear_out(float4* __restrict__ gout, const uint32_t* __restrict__ list, uint32_t* count,
+                                                       int n, int nb, uint32_t* stamp, DevCounters* cnt, uint32_t* done) {
+    const int64_t total = (int64_t)(*count) * 64;
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        uint32_t b = list[i >> 6];
+        int l = (int)(i & 63);
+        int bz = b % nb, by = (b / nb) % nb, bx = b / (nb * nb);
+        int ix = 4 * bx + (l >> 4), iy = 4 * by + ((l >> 2) & 3), iz = 4 * bz + (l & 3);
+        if (ix < n && iy < n && iz < n) gout[((size_t)ix * n + iy) * n + iz] = z;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(done, 1u) == gridDim.x - 1) {
+            *done = 0u;
+            *stamp += 1u;
+            cnt->n_items = 0u; cnt->n_active_blocks = 0u; cnt->n_tiles = 0u; cnt->n_clamped = 0u;
+            cnt->p2g_cursor = 0u; cnt->g2p_cursor = 0u; cnt->n_cross = 0u; cnt->list_stamp = *stamp;
+            *count = 0u;
+        }
+    }
+}
+
+// classic -> lagged: the last (classic) substep left its scatter in grid_in and its velocities in grid_out over block
+// list [l], and used up the cursors of its work list; the lagged substep that follows runs on that same work list
+// and block list, from a clean grid
+__global__ void __launch_bounds__(256) k_lag_enter(float4* __restrict__ gin, float4* __restrict__ gout, const uint32_t* __restrict__ list,
+                                                   const uint32_t* __restrict__ count, int n, int nb, const uint32_t* stamp, DevCounters* cnt) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        cnt->p2g_cursor = 0u; cnt->g2p_cursor = 0u; cnt->n_cross = 0u; cnt->n_clamped = 0u; cnt->list_stamp = *stamp;
+    }
+    const int64_t total = (int64_t)(*count) * 64;
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        uint32_t b = list[i >> 6];
+        int l = (int)(i & 63);
+        int bz = b % nb, by = (b / nb) % nb, bx = b / (nb * nb);
+        int ix = 4 * bx + (l >> 4), iy = 4 * by + ((l >> 2) & 3), iz = 4 * bz + (l & 3);
+        if (ix < n && iy < n && iz < n) {
+            const size_t node = ((size_t)ix * n + iy) * n + iz;
+            gin[node] = z; gout[node] = z;
+        }
+    }
+}
+
+// grid_in over block list [cur_list], zeroed beside g2p (which only reads grid_out) for the next substep's scatter.
+// (Zeroing it behind the grid pass, in k_grid, makes that kernel five times slower -- 12 -> 60 us on S-4M.)
+__global__ void __launch_bounds__(256) k_lag_clear_in(float4* __restrict__ gin, const uint32_t* __restrict__ list, const uint32_t* __restrict__ count,
+                                                      int n, int nb) {
+    const int64_t total = (int64_t)(*count) * 64;
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        uint32_t b = list[i >> 6];
+        int l = (int)(i & 63);
+        int bz = b % nb, by = (b / nb) % nb, bx = b / (nb * nb);
+        int ix = 4 * bx + (l >> 4), iy = 4 * by + ((l >> 2) & 3), iz = 4 * bz + (l & 3);
+        if (ix < n && iy < n && iz < n) gin[((size_t)ix * n + iy) * n + iz] = z;
+    }
+}
+
+int mpmk_launch_lag_clear_in(mpmk_ctx* ctx, cudaStream_t s) {
+    const int l = ctx->cur_list;
+    mpmk_launch(k_lag_clear_in, dim3(ctx->sm_count * 2), dim3(256), 0, s, (float4*)ctx->b.grid_in, ctx->block_list[l], ctx->block_count[l], ctx->n_grid, ctx->nb);
+    MPMK_LAUNCH_CHECK(ctx);
+    return 0;
+}
+
+int mpmk_worklist_init(mpmk_ctx* ctx) {
+    // side-branch kernels of a lagged batch share SMs with the persistent p2g / g2p grids: same shared-memory carve-out
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_lag_clear_in, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_lag_clear_out, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_tile_runs, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_build_items<1>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_build_items<32>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    return 0;
+}
+
+// precondition: ctx->coherent after a classic substep (work list [wl] and block list [cur_list] describe the current
+// physical order).  Leaves the context as a lagged substep leaves it: the lists to use next are the "other" ones.
+int mpmk_launch_lag_enter(mpmk_ctx* ctx, cudaStream_t s) {
+    const int l = ctx->cur_list;
+    mpmk_launch(k_lag_enter, dim3(ctx->sm_count * 8), dim3(256), 0, s, (float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out, ctx->block_list[l],
+                ctx->block_count[l], ctx->n_grid, ctx->nb, ctx->dev_stamp, ctx->counters_buf[ctx->wl]);
+    MPMK_LAUNCH_CHECK(ctx);
+    use_worklist(ctx, 1 - ctx->wl);
+    ctx->cur_list = 1 - l;
+    ctx->lag_ready = true;
+    return 0;
+}
+
+// start of a lagged substep (host side): the prebuilt lists become the current ones
+void mpmk_lag_flip(mpmk_ctx* ctx) {
+    use_worklist(ctx, 1 - ctx->wl);
+    ctx->cur_list = 1 - ctx->cur_list;
+}
+
+// side branch, first kernel: grid_out of the substep before this one, and the reset for the rebuild
+int mpmk_launch_lag_clear_out(mpmk_ctx* ctx, cudaStream_t s) {
+    const int l = 1 - ctx->cur_list, w = 1 - ctx->wl;
+    mpmk_launch(k_lag_clear_out, dim3(ctx->sm_count * 2), dim3(256), 0, s, (float4*)ctx->b.grid_out, ctx->block_list[l], ctx->block_count[l], ctx->n_grid,
+                ctx->nb, ctx->dev_stamp, ctx->counters_buf[w], ctx->lag_done);
+    MPMK_LAUNCH_CHECK(ctx);
+    return 0;
+}
+
+// side branch, after the sort: lists for the NEXT substep into the other set
+int mpmk_launch_prepare_lagged(mpmk_ctx* ctx, cudaStream_t s) {
+    return launch_build(ctx, 1 - ctx->wl, 1 - ctx->cur_list, s);
 }

@@ -54,6 +54,12 @@ def main():
     torch.cuda.synchronize()
     graph_ms = e0.elapsed_time(e1) / a.reps
     b = sim._backend
+    trace = None
+    if os.environ.get("MPMK_TRACE"):
+        buf = (C.c_ulonglong * 16)()
+        b.ctx.call("mpmk_debug_trace", C.cast(buf, C.c_void_p))
+        t0 = buf[0]
+        trace = {k: round((buf[i] - t0) / 1e3, 1) for k, i in (("p2g_done", 1), ("grid_done", 2), ("g2p_done", 3), ("side_clear", 5), ("side_sort", 6), ("side_lists", 7))}
     sops = sim._ops_at(sim.time)
     stages = ["sort", "prepare", "p2g", "grid", "g2p"]
     acc = {k: 0.0 for k in stages}
@@ -73,7 +79,7 @@ def main():
             acc[k] += evs[r][i].elapsed_time(evs[r][i + 1]) / a.reps
     out = {"tag": a.tag, "workload": a.workload, "material": args.material, "n": n, "graph_ms_per_substep": round(graph_ms, 4),
            "Gpss": round(n / graph_ms / 1e6, 3), "stage_ms": {k: round(v, 4) for k, v in acc.items()},
-           "counters": sim.counters(), "finite": bool(torch.isfinite(sim.export()[0]).all())}
+           "trace_us": trace, "counters": sim.counters(), "finite": bool(torch.isfinite(sim.export()[0]).all())}
     print(json.dumps(out), flush=True)
 
 

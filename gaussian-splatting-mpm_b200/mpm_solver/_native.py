@@ -13,7 +13,7 @@ _ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB_PATH = os.environ.get("MPMK_LIB") or os.path.join(_ROOT, "lib", "libmpmk.so")
 
 MAT_JELLY, MAT_METAL, MAT_SAND, MAT_FOAM, MAT_FLUID, MAT_PLASTICINE = range(6)
-STRICT_Q1, STRICT_Q3, WRITE_FTRIAL, TRACK_COV, SORT_FULL, SORT_MERGE = 1, 2, 4, 8, 16, 64
+STRICT_Q1, STRICT_Q3, WRITE_FTRIAL, TRACK_COV, SORT_FULL, SORT_MERGE, NO_LAG = 1, 2, 4, 8, 16, 64, 128
 OP_FIXED_CUBE, OP_COLLIDER = 0, 1
 MAX_GRID_OPS, MAX_IMPULSES = 16, 8
 
@@ -54,7 +54,7 @@ class WorldXform(C.Structure):
 
 class Counters(C.Structure):
     _fields_ = [("n_items", C.c_uint32), ("n_active_blocks", C.c_uint32), ("n_tiles", C.c_uint32),
-                ("n_clamped", C.c_uint32)]
+                ("n_clamped", C.c_uint32), ("n_crossers", C.c_uint32)]
 
 
 class MpmkError(RuntimeError):
@@ -109,6 +109,8 @@ def lib():
         "mpmk_constitutive_ex": (i, [vp, f, i, i, vp]),
         "mpmk_sort": (i, [vp, vp]),
         "mpmk_get_sort_result": (i, [vp, vp, vp, vp]),
+        "mpmk_get_last_sort": (i, [vp, vp, vp, vp, vp]),
+        "mpmk_debug_trace": (i, [vp, vp]),
         "mpmk_sort_info": (i, [vp, C.POINTER(i), C.POINTER(i64), vp]),
         "mpmk_prepare_grid": (i, [vp, vp]),
         "mpmk_p2g": (i, [vp, f, C.POINTER(SubstepOps), vp]),

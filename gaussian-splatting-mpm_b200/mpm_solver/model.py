@@ -307,6 +307,19 @@ class _FTrialField(FieldView):
         return super()._gather_sorted()
 
 
+class _YieldStressField(FieldView):
+    """model.yield_stress as the reference holds it between substeps.  The library runs the return mapping of F_trial(s)
+    in the epilogue of substep s (the reference: at the start of substep s+1, utils.py:14-54), so f2.w is one hardening /
+    softening update ahead of the reference's field; the last g2p of a batch keeps the value from BEFORE that update next
+    to F_trial (ft2.y), and that is what a reader gets while it is valid."""
+
+    def _gather_sorted(self):
+        b = self._b
+        if b.ftrial_valid():
+            return b.ft[2][: b.n, 1:2]
+        return super()._gather_sorted()
+
+
 class _ExportField:
     """particle_xyz / particle_cov / particle_R: produced by the export kernel straight into
     persistent torch buffers in original order (the zero-copy hand-off to the rasterizer that
@@ -442,7 +455,7 @@ class MPM_model:
 
     def init_other_params(self):  # model.py:53-59
         b = self._backend
-        self.yield_stress = FieldView(b, [("f2", 3)], (), after_write=lambda: b.mark_stress_dirty(ys_written=True))
+        self.yield_stress = _YieldStressField(b, [("f2", 3)], (), after_write=lambda: b.mark_stress_dirty(ys_written=True))
         self.yield_stress.fill(0.005)
         self.hardening = 1
         self.xi = 1

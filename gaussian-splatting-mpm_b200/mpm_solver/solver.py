@@ -66,6 +66,7 @@ class MPM_Simulator:
         self._track_cov = track_cov
         self._sort_full = False
         self._sort_merge = False
+        self._no_lag = False
         self._sync_flags()
 
     def load_particles(self, xyzs, covs, volumes):
@@ -100,6 +101,8 @@ class MPM_Simulator:
             f |= _native.SORT_FULL
         if self._sort_merge:
             f |= _native.SORT_MERGE
+        if self._no_lag:
+            f |= _native.NO_LAG
         if self._has_plastic():
             f |= _native.WRITE_FTRIAL  # F_trial != F after a return mapping; export needs F_trial
         self._backend.params.flags = f
@@ -109,7 +112,8 @@ class MPM_Simulator:
         """Update solver parameters from a dict (not in the reference; north_star asks for it).
         Keys: gravity, E, nu, yield_stress, hardening, xi, plastic_viscosity, softening, friction_angle,
         strict_q1, strict_q3, track_cov, sort_full (always the full radix sort, never the merge of the movers), sort_merge (the merge whenever valid,
-        also for small clouds).  The physics keys take effect from the next substep on, as they would in the reference, whose
+        also for small clouds), no_lag (step() keeps the sort on the critical path of every substep instead of running it beside p2g
+        on the previous substep's work list).  The physics keys take effect from the next substep on, as they would in the reference, whose
         p2g2p re-evaluates the stress from F_trial with the current parameters (solver.py:36)."""
         p = dict(params or {})
         p.update(kw)
@@ -129,7 +133,7 @@ class MPM_Simulator:
                 m._logE.fill_(math.log10(v))
             elif k == "nu":
                 m._y.fill_(-math.log(0.49 / v - 1))
-            elif k in ("strict_q1", "strict_q3", "track_cov", "sort_full", "sort_merge"):
+            elif k in ("strict_q1", "strict_q3", "track_cov", "sort_full", "sort_merge", "no_lag"):
                 setattr(self, "_" + k, bool(v))
             else:
                 raise KeyError(k)

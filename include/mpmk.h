@@ -54,6 +54,7 @@ extern "C" {
 #define MPMK_TRACK_COV 8u  /* g2p applies update_cov every substep (utils.py:187-215) */
 #define MPMK_SORT_MERGE 64u /* take the merge path whenever it is valid, also below the size where it pays (tests) */
 #define MPMK_SORT_FULL 16u /* always run the full radix sort (no merge of the few particles that changed cell) */
+#define MPMK_NO_LAG 128u   /* mpmk_substeps: keep the sort on the critical path in every substep (see api.cu, lagged substeps) */
 
 typedef struct mpmk_ctx mpmk_ctx;
 
@@ -131,6 +132,7 @@ typedef struct {
     uint32_t n_active_blocks; /* 4x4x4-node blocks touched by p2g              */
     uint32_t n_tiles;         /* non-empty 4x4x4-cell tiles                    */
     uint32_t n_clamped;       /* particles whose base cell was clamped (Q9)    */
+    uint32_t n_crossers;      /* lagged substeps: particles whose cell had left their work item's tile */
 } mpmk_counters;
 
 /* ---- lifecycle ---------------------------------------------------------- */
@@ -264,7 +266,16 @@ MPMK_API int mpmk_mg_peer_close(mpmk_ctx* ctx);
 /* the halo sum alone (stagewise use: after mpmk_p2g, before mpmk_grid_update)     */
 MPMK_API int mpmk_mg_halo_exchange(mpmk_ctx* ctx, void* stream);
 
+/* The most recent sort, wherever it ran (mpmk_sort, or the side branch of a lagged substep inside mpmk_substeps):
+ * sorted keys, the permutation (physical slot, AT THE TIME OF THAT SORT, of the r-th particle in sorted order) and --
+ * lagged substeps only -- its inverse, the slot g2p moved each particle to.  Any pointer may be NULL.  For tests. */
+MPMK_API int mpmk_get_last_sort(mpmk_ctx* ctx, void* sorted_keys_dev, void* perm_dev, void* rank_dev, void* stream);
+
 /* ---- introspection -------------------------------------------------------- */
+/* With MPMK_TRACE=1 in the environment: %globaltimer (ns) at the stage boundaries of the last lagged substep of the last
+ * batch -- [0] start, [1] p2g done, [2] grid done, [3] g2p done; side branch [5] clear done, [6] sort done, [7] work
+ * lists done.  Synchronises the device.  Tuning aid. */
+MPMK_API int mpmk_debug_trace(mpmk_ctx* ctx, unsigned long long* out16);
 /* synchronises `stream` */
 MPMK_API int mpmk_read_counters(mpmk_ctx* ctx, mpmk_counters* out, void* stream);
 /* how many kernels the library has launched since create (for bench's gpu_launches) */
