@@ -41,7 +41,7 @@ static int create_impl(mpmk_ctx* ctx, int device, int n_grid, double grid_extent
     ALLOC0(ctx, ctx->perm, cap * 4);
     ALLOC0(ctx, ctx->perm_alt, cap * 4);
     ctx->n_sort_ctas_cap = div_up((int64_t)cap, MPMK_SORT_CHUNK);
-    ALLOC0(ctx, ctx->sort_ctrl, ((size_t)8 + 4 * 512 + ((size_t)4 * (1 << MPMK_MAX_RADIX_BITS) + 2) * ctx->n_sort_ctas_cap) * 4);
+    ALLOC0(ctx, ctx->sort_ctrl, ((size_t)8 + 4 * 512 + ((size_t)2 * 4 * (1 << MPMK_MAX_RADIX_BITS) + 2) * (ctx->n_sort_ctas_cap + 1)) * 4);   // (x 2: the lean mover passes of a lagged batch use 2048-key tiles)
     for (int i = 0; i < 2; ++i) { ALLOC0(ctx, ctx->cs_mk[i], cap * 4); ALLOC0(ctx, ctx->cs_mv[i], cap * 4); }
     ALLOC0(ctx, ctx->cs_mask, (cap / 32 + 2) * 4);
     ALLOC0(ctx, ctx->cs_mprefix, (cap / 32 + 2) * 4);
@@ -56,7 +56,6 @@ static int create_impl(mpmk_ctx* ctx, int device, int n_grid, double grid_extent
     ctx->wl = 0; ctx->items = ctx->items_buf[0]; ctx->counters = ctx->counters_buf[0];
     ALLOC0(ctx, ctx->rank, cap * 4);
     ALLOC0(ctx, ctx->keys_b, cap * 4);
-    ALLOC0(ctx, ctx->cross_list, cap * 4);
     ALLOC0(ctx, ctx->lag_done, 4);
     ALLOC0(ctx, ctx->trace, 16 * sizeof(unsigned long long));
     ALLOC0(ctx, ctx->tile_list, ((cap < ntiles ? cap : ntiles) + 8) * sizeof(uint2));
@@ -103,7 +102,7 @@ extern "C" int mpmk_destroy(mpmk_ctx* ctx) {
     cudaFree(ctx->sort_ctrl); cudaFree(ctx->hist_tot); cudaFree(ctx->tile_list); cudaFree(ctx->tile_end);
     for (int i = 0; i < 2; ++i) { cudaFree(ctx->items_buf[i]); cudaFree(ctx->counters_buf[i]); cudaFree(ctx->block_stamp[i]); }
     cudaFree(ctx->block_list[0]); cudaFree(ctx->block_list[1]); cudaFree(ctx->block_count[0]); cudaFree(ctx->block_count[1]);
-    cudaFree(ctx->dev_stamp); cudaFree(ctx->rank); cudaFree(ctx->keys_b); cudaFree(ctx->cross_list); cudaFree(ctx->lag_done); cudaFree(ctx->trace);
+    cudaFree(ctx->dev_stamp); cudaFree(ctx->rank); cudaFree(ctx->keys_b); cudaFree(ctx->lag_done); cudaFree(ctx->trace);
     if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
     if (ctx->side_stream) cudaStreamDestroy(ctx->side_stream);
     if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
@@ -235,7 +234,7 @@ extern "C" int mpmk_substep(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops
 // previous substep (g2p writes it), and one substep moves ~3.5 % of the particles to another cell and ~1 % to
 // another tile, so p2g and g2p of substep s run on the work list built from the sort of substep s-1: the true cell of
 // a particle comes from its current key; one that left its item's tile scatters straight to the global grid and
-// gathers from it (k_g2p_cross).  Meanwhile, on a forked branch of the graph, the sort of substep s (still the
+// gathers from it.  Meanwhile, on a forked branch of the graph, the sort of substep s (still the
 // bit-exact stable sort of the current keys), the work list and the block list for substep s+1 are built; g2p joins
 // that branch and writes every particle to the slot its rank says, which re-establishes physical order == sorted
 // order of substep s.  The clear pass disappears as well: the grid pass zeroes grid_in behind itself and the side
@@ -257,7 +256,8 @@ static bool trace_enabled() {
     static const bool on = getenv("MPMK_TRACE") && atoi(getenv("MPMK_TRACE")) != 0;
     return on;
 }
-#define TRACE(ctx, stream, slot) do { if (trace_enabled()) k_trace_stamp<<<1, 1, 0, (stream)>>>((ctx)->trace, (slot)); } while (0)
+void mpmk_trace(mpmk_ctx* ctx, cudaStream_t s, int slot) { if (trace_enabled()) k_trace_stamp<<<1, 1, 0, s>>>(ctx->trace, slot); }
+#define TRACE(ctx, stream, slot) mpmk_trace(ctx, stream, slot)
 
 extern "C" int mpmk_debug_trace(mpmk_ctx* ctx, unsigned long long* out16) {
     if (!ctx || !out16) return MPMK_ERR_INVALID;

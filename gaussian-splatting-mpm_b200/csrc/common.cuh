@@ -32,7 +32,7 @@ struct DevCounters {
     uint32_t n_clamped;
     uint32_t p2g_cursor;   // dynamic work fetch
     uint32_t g2p_cursor;
-    uint32_t n_cross;      // lagged batches: particles whose cell left their work item's tile (g2p defers them to k_g2p_cross)
+    uint32_t n_cross;      // lagged batches: particles whose cell left their work item's tile (p2g scatters them straight to the global grid, g2p gathers from it)
     uint32_t list_stamp;   // lagged batches: stamp value of the block list this work list goes with
 };
 
@@ -109,7 +109,6 @@ struct mpmk_ctx {
     uint32_t* rank;          // inverse of perm: sorted position of each physical slot (g2p's destination slot)
     uint32_t* keys_b;        // second key buffer: g2p reads the keys of its source slots while it writes the next ones
     uint32_t* keys_cur;      // the buffer holding the current keys: b.keys at every API boundary, keys_b inside a batch
-    uint32_t* cross_list;    // physical slots of the particles g2p deferred (their cell lies outside the item's tile)
     bool lag_ready;          // set [1-wl] / list [1-cur_list] are prebuilt for the current physical order, grid_in is clean
     uint32_t* lag_done;      // device scalar: CTAs of k_lag_clear_out that have finished
     unsigned long long* trace;  // MPMK_TRACE: %globaltimer stamps of the last lagged substep (api.cu)
@@ -285,6 +284,7 @@ int mpmk_launch_grid_lagged(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops
 int mpmk_launch_g2p_lagged(mpmk_ctx* ctx, float dt, cudaStream_t s);
 int mpmk_launch_sort_lagged(mpmk_ctx* ctx, cudaStream_t s);
 void mpmk_lag_flip(mpmk_ctx* ctx);
+void mpmk_trace(mpmk_ctx* ctx, cudaStream_t s, int slot);
 int mpmk_item_size(const mpmk_ctx* ctx);
 int mpmk_launch_p2g(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);
 int mpmk_launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cudaStream_t s);

@@ -25,7 +25,6 @@ struct G2PArgs {
     const uint4* items;
     const float4* grid_out;
     DevCounters* cnt;
-    uint32_t* cross;         // LAG: physical slots deferred to k_g2p_cross
     int64_t n;
     int n_grid, nt;
     float inv_dx, dt;
@@ -44,7 +43,7 @@ __device__ __forceinline__ void bspline(float f, float* w, float* dw) {
 }
 
 // One particle: gather from the 3x3x3 nodes at g (x stride sx, y stride sy float4s: the warp's shared tile, or the
-// global grid for a crosser), then everything utils.py:255-279 and the next substep's utils.py:14-54 do with it.
+// global grid for a particle whose cell left the item's tile), then everything utils.py:255-279 and the next substep's utils.py:14-54 do with it.
 // src / dst: the particle's slot in the source / destination set; pF0..pMeta: its records (shared stage or global).
 __device__ __forceinline__ void g2p_particle(const G2PArgs& a, const uint32_t src, const uint32_t dst, const float4 X, const float fx,
                                              const float fy, const float fz, const float4* __restrict__ g, const int sx, const int sy,
@@ -183,8 +182,8 @@ __device__ __forceinline__ void g2p_particle(const G2PArgs& a, const uint32_t sr
 //
 // LAG = true (lagged batches, api.cu): the work list comes from the sort of the previous substep, batches are 32
 // consecutive physical slots, the true cell comes from the current key, and the particle is written to the slot the
-// sort of THIS substep (done on the side branch by now) ranks it at.  Particles whose cell left the item's tile are
-// handed to k_g2p_cross, which gathers from the global grid.
+// sort of THIS substep (done on the side branch by now) ranks it at.  Particles whose cell left the item's tile gather
+// from the global grid instead of the warp's tile (same code: the gather pointer is per lane).
 #ifndef G2P_WARPS
 #define G2P_WARPS 4
 #endif
@@ -273,15 +272,26 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
         if (lane < dA.count) {
             const uint32_t r = dA.base + lane;
             const uint32_t key = S.key[kslot][lane];
+            const float4 X = S.rec[stage][0][lane];
+            int bx = 4 * tx + (int)((key >> 4) & 3), by = 4 * ty + (int)((key >> 2) & 3), bz = 4 * tz + (int)(key & 3);   // base cell
+            const float4* g = S.tile + (((key >> 4) & 3) * 36 + ((key >> 2) & 3) * 6 + (key & 3));
+            int sx = 36, sy = 6;
             if (LAG && (key >> 6) != dA.tile) {
-                a.cross[atomicAdd(&a.cnt->n_cross, 1u)] = r;   // its cell left this tile: k_g2p_cross gathers from the global grid
-            } else {
-                const float4 X = S.rec[stage][0][lane];
-                const int lx = (key >> 4) & 3, ly = (key >> 2) & 3, lz = key & 3;
-                const float fx = __fmul_rn(X.x, a.inv_dx) - (float)(4 * tx + lx);
-                const float fy = __fmul_rn(X.y, a.inv_dx) - (float)(4 * ty + ly);
-                const float fz = __fmul_rn(X.z, a.inv_dx) - (float)(4 * tz + lz);
-                g2p_particle(a, LAG ? r : pA, LAG ? pA : r, X, fx, fy, fz, S.tile + (lx * 36 + ly * 6 + lz), 36, 6, &S.rec[stage][1][lane],
+                // its cell left this item's tile since the work list was built (~0.2 % of the particles): the same gather, from
+                // the global grid (generic loads serve both: the tile pointer is a generic address too)
+                const uint32_t tt = key >> 6;
+                bx = 4 * (int)(tt / (uint32_t)(a.nt * a.nt)) + (int)((key >> 4) & 3);
+                by = 4 * (int)((tt / (uint32_t)a.nt) % (uint32_t)a.nt) + (int)((key >> 2) & 3);
+                bz = 4 * (int)(tt % (uint32_t)a.nt) + (int)(key & 3);
+                g = a.grid_out + (((size_t)bx * n + by) * n + bz);
+                sx = n * n; sy = n;
+                atomicAdd(&a.cnt->n_cross, 1u);
+            }
+            {
+                const float fx = __fmul_rn(X.x, a.inv_dx) - (float)bx;
+                const float fy = __fmul_rn(X.y, a.inv_dx) - (float)by;
+                const float fz = __fmul_rn(X.z, a.inv_dx) - (float)bz;
+                g2p_particle(a, LAG ? r : pA, LAG ? pA : r, X, fx, fy, fz, g, sx, sy, &S.rec[stage][1][lane],
                              &S.rec[stage][2][lane], &S.rec[stage][3][lane], reinterpret_cast<const int4*>(&S.rec[stage][4][lane]));
             }
         }
@@ -293,26 +303,6 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
         kslot = (kslot + 1) % 3;
     }
     cp_async_wait<0>();
-}
-
-// lagged batches: the particles k_g2p<true> deferred, one per thread, stencil nodes straight from the global grid
-__global__ void __launch_bounds__(128) k_g2p_cross(const G2PArgs a) {
-    const uint32_t nc = a.cnt->n_cross;
-    const int n = a.n_grid;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nc; i += gridDim.x * blockDim.x) {
-        const uint32_t r = a.cross[i];
-        const uint32_t key = a.skeys[r];
-        const uint32_t tt = key >> 6;
-        const int bx = 4 * (int)(tt / (uint32_t)(a.nt * a.nt)) + (int)((key >> 4) & 3);
-        const int by = 4 * (int)((tt / (uint32_t)a.nt) % (uint32_t)a.nt) + (int)((key >> 2) & 3);
-        const int bz = 4 * (int)(tt % (uint32_t)a.nt) + (int)(key & 3);
-        const float4 X = a.xm[r];
-        const float fx = __fmul_rn(X.x, a.inv_dx) - (float)bx;
-        const float fy = __fmul_rn(X.y, a.inv_dx) - (float)by;
-        const float fz = __fmul_rn(X.z, a.inv_dx) - (float)bz;
-        g2p_particle(a, r, a.perm[r], X, fx, fy, fz, a.grid_out + (((size_t)bx * n + by) * n + bz), n * n, n, a.f0 + r, a.f1 + r, a.f2 + r,
-                     a.meta + r);
-    }
 }
 
 // utils.py:14-54 on the current set in place (init, and after from_torch edits of F)
@@ -378,7 +368,6 @@ static int launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s, bool lag) {
         a.ft0 = (float4*)ctx->b.ft0; a.ft1 = (float4*)ctx->b.ft1; a.ft2 = (float4*)ctx->b.ft2;
         a.items = ctx->items;
         a.okeys = keys_out; a.grid_out = (const float4*)ctx->b.grid_out; a.cnt = ctx->counters;
-        a.cross = ctx->cross_list;
         a.n = ctx->n; a.n_grid = ctx->n_grid; a.nt = ctx->nt; a.inv_dx = ctx->inv_dx; a.dt = dt;
         a.cp = make_cp(ctx);
         if ((a.cp.flags & MPMK_TRACK_COV) && (!A.cv0 || !A.cv1 || !B.cv0 || !B.cv1))
@@ -391,8 +380,7 @@ static int launch_g2p(mpmk_ctx* ctx, float dt, cudaStream_t s, bool lag) {
         const dim3 grid((int)(want < cap ? want : cap));
         if (lag) {
             mpmk_launch(k_g2p<true>, grid, dim3(G2P_WARPS * 32), sizeof(G2PWarpSmem) * G2P_WARPS, s, a);
-            MPMK_LAUNCH_CHECK(ctx);
-            k_g2p_cross<<<ctx->sm_count, 128, 0, s>>>(a);
+
         } else {
             mpmk_launch(k_g2p<false>, grid, dim3(G2P_WARPS * 32), sizeof(G2PWarpSmem) * G2P_WARPS, s, a);
         }

@@ -28,12 +28,11 @@
 #define P2G_WARPS 4
 #endif
 #ifndef P2G_MIN_CTAS
-#define P2G_MIN_CTAS 4
+#define P2G_MIN_CTAS 5   // caps the kernel at 96 registers (113 without: four CTAs would then leave nothing for the side branch of a lagged batch)
 #endif
 #define P2G_REC_STRIDE 33  // float4 per record slot: 32 lanes + 1 pad (bank-conflict-free phase B reads)
 #define P2G_REC_SLOTS 12   // 9 x {Y_ij.xyz, wx_i wy_j} + 3 x {R_k.xyz, wz_k}
 
-#define P2G_NSTAGE 6       // xm, vv, c0, c1, cs, s1
 #define P2G_TILE_SX 37     // x stride of the shared tile in float4 (6*6 + 1 pad)
 #define P2G_TILE_F4 (6 * P2G_TILE_SX)
 
@@ -46,7 +45,6 @@ __constant__ unsigned char P2G_LANE_NODE[32] = {2, 1, 11, 19, 9, 10, 21, 13, 24,
 struct __align__(16) P2GWarpSmem {
     float4 rec[P2G_REC_SLOTS * P2G_REC_STRIDE];
     float4 tile[P2G_TILE_F4];
-    float4 stage[P2G_NSTAGE][32];  // next batch's particle records, in flight (cp.async) while this batch is scattered
 };
 
 #define P2G_CROSS 0x40000000   // cell code of a crosser: P2G_CROSS | bx | by << 10 | bz << 20 (base cell, n_grid <= 1023)
@@ -100,8 +98,7 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
     const int ni = node / 9, nj = (node / 3) % 3, nk = node % 3;
     const int nij = ni * 3 + nj;
     const int noff = ni * P2G_TILE_SX + nj * 6 + nk;
-    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int i = lane; i < P2G_TILE_F4; i += 32) S.tile[i] = zero4;
+    for (int i = lane; i < P2G_TILE_F4; i += 32) S.tile[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     __syncwarp();
     const int n = a.n_grid;
 
@@ -118,12 +115,15 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
     if (lane < dA.count) { pA = LAG ? dA.base + lane : a.perm[dA.base + lane]; kA = a.skeys[dA.base + lane]; }
     BatchDesc dB = bs.next(lane, a.items, &a.cnt->p2g_cursor, n_items);
     if (lane < dB.count) { pB = LAG ? dB.base + lane : a.perm[dB.base + lane]; kB = a.skeys[dB.base + lane]; }
+    // the next batch's particle records travel in registers (six 16-byte loads per lane, issued before phase B of the
+    // current batch, which needs few registers and runs for hundreds of cycles): no shared-memory staging, which cost
+    // 1.5 of the kernel's 12.4 shared-memory wavefronts per particle and 3 KB of shared memory per warp
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 Xn = zero4, Vn = zero4, C0n = zero4, C1n = zero4, CSn = zero4, S1n = zero4;
     if (lane < dA.count) {
-        cp_async16(&S.stage[0][lane], a.xm + pA); cp_async16(&S.stage[1][lane], a.vv + pA);
-        cp_async16(&S.stage[2][lane], a.c0 + pA); cp_async16(&S.stage[3][lane], a.c1 + pA);
-        cp_async16(&S.stage[4][lane], a.cs + pA); cp_async16(&S.stage[5][lane], a.s1 + pA);
+        Xn = __ldg(a.xm + pA); Vn = __ldg(a.vv + pA); C0n = __ldg(a.c0 + pA);
+        C1n = __ldg(a.c1 + pA); CSn = __ldg(a.cs + pA); S1n = __ldg(a.s1 + pA);
     }
-    cp_async_commit();
     int cur_cell = -1;
     float4 acc = zero4, acc2 = zero4;
     int tx = 0, ty = 0, tz = 0;
@@ -132,19 +132,7 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
         if (dA.first) { tz = dA.tile % a.nt; ty = (dA.tile / a.nt) % a.nt; tx = dA.tile / (a.nt * a.nt); }
         const int nbatch = dA.count;
             int my_cell = 64;  // lanes past the end of the batch never match a real cell
-            cp_async_wait<0>();
-            float4 X = zero4, V = zero4, C0 = zero4, C1 = zero4, CS = zero4, S1 = zero4;
-            if (lane < nbatch) {
-                X = S.stage[0][lane]; V = S.stage[1][lane]; C0 = S.stage[2][lane];
-                C1 = S.stage[3][lane]; CS = S.stage[4][lane]; S1 = S.stage[5][lane];
-            }
-            // the stage slots are free again: start batch B's records, then batch C's permutation entries
-            if (lane < dB.count) {
-                cp_async16(&S.stage[0][lane], a.xm + pB); cp_async16(&S.stage[1][lane], a.vv + pB);
-                cp_async16(&S.stage[2][lane], a.c0 + pB); cp_async16(&S.stage[3][lane], a.c1 + pB);
-                cp_async16(&S.stage[4][lane], a.cs + pB); cp_async16(&S.stage[5][lane], a.s1 + pB);
-            }
-            cp_async_commit();
+            const float4 X = Xn, V = Vn, C0 = C0n, C1 = C1n, CS = CSn, S1 = S1n;
             const BatchDesc dC = bs.next(lane, a.items, &a.cnt->p2g_cursor, n_items);
             if (lane < dC.count) { pC = LAG ? dC.base + lane : a.perm[dC.base + lane]; kC = a.skeys[dC.base + lane]; }
             // ---------------- phase A: lane = particle ----------------
@@ -230,6 +218,11 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
                     rw.w = wz[k];
                     S.rec[(9 + k) * P2G_REC_STRIDE + lane] = rw;
                 }
+            }
+            // batch B's records: in flight during phase B
+            if (lane < dB.count) {
+                Xn = __ldg(a.xm + pB); Vn = __ldg(a.vv + pB); C0n = __ldg(a.c0 + pB);
+                C1n = __ldg(a.c1 + pB); CSn = __ldg(a.cs + pB); S1n = __ldg(a.s1 + pB);
             }
             __syncwarp();
             // ---------------- phase B: lane = stencil node ----------------
@@ -332,7 +325,11 @@ int mpmk_p2g_init(mpmk_ctx* ctx) {
     MPMK_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_p2g<true>, P2G_WARPS * 32, smem));
     ctx->p2g_lag_ctas_per_sm = per_sm > 0 ? per_sm : 1;
     // the side branch (sort + work lists of the next substep) needs room beside the persistent scatter grid
-    static const int leave = getenv("MPMK_LAG_P2G_CTAS") ? atoi(getenv("MPMK_LAG_P2G_CTAS")) : 0;
+    // (4 CTAs of 128 threads x 96 registers and 39.5 KB leave 16 K registers and 66 KB per SM: one 256-thread CTA of
+    // every side-branch kernel)
+    static const int leave = getenv("MPMK_LAG_P2G_CTAS") ? atoi(getenv("MPMK_LAG_P2G_CTAS")) : 4;
     if (leave > 0 && leave < ctx->p2g_lag_ctas_per_sm) ctx->p2g_lag_ctas_per_sm = leave;
+    static const int classic = getenv("MPMK_P2G_CTAS") ? atoi(getenv("MPMK_P2G_CTAS")) : 0;
+    if (classic > 0 && classic < ctx->p2g_ctas_per_sm) ctx->p2g_ctas_per_sm = classic;
     return 0;
 }

@@ -158,8 +158,7 @@ __global__ void __launch_bounds__(CTA) k_sort_onesweep(const uint32_t* __restric
                                                                  uint32_t* __restrict__ status, uint32_t* __restrict__ tile_counter) {
     pdl_wait();   // programmatic dependent launch: nothing of the previous grid is read or overwritten before this
     constexpr int D = 1 << BITS;
-    constexpr int CHUNK = CTA * ROUNDS;
-    static_assert(CHUNK == MPMK_SORT_CHUNK, "tile size is part of the control block layout");
+    constexpr int CHUNK = CTA * ROUNDS;   // (the host sizes the status words of a pass by the tile count of this CHUNK)
     constexpr int NW = CTA / 32;
     constexpr int DPT = (D + CTA - 1) / CTA;  // digits per thread (1 or 2)
     __shared__ uint32_t lstart[D];   // tile-local first position of digit d
@@ -609,7 +608,8 @@ static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s, bool want_ra
     constexpr int D = 1 << BITS;
     const int ntiles = div_up(ctx->n, MPMK_SORT_CHUNK);   // == chunks of the scans (CS_CHUNK == MPMK_SORT_CHUNK)
     static_assert(CS_CHUNK == MPMK_SORT_CHUNK, "the scans and the radix tiles share the control block sizing");
-    const size_t radix_status = (size_t)passes * ntiles * D;
+    const int mtiles = want_rank ? div_up(ctx->n, 2048) : ntiles;   // tiles of the movers' radix passes (lean variant: 2048 keys)
+    const size_t radix_status = (size_t)passes * mtiles * D;
     const size_t ctrl_words = OS_CTRL_STATUS + radix_status + 2 * (size_t)ntiles;
     MPMK_CHECK(ctx, cudaMemsetAsync(ctx->sort_ctrl, 0, ctrl_words * 4, s));
     uint32_t* ctrl = ctx->sort_ctrl;
@@ -622,23 +622,32 @@ static int sort_coherent(mpmk_ctx* ctx, int passes, cudaStream_t s, bool want_ra
     mpmk_launch(k_cs_flag_scan, dim3(min(ntiles, ctx->sm_count * 5)), dim3(CS_THREADS), 0, s, keys, okeys, ctx->n, ctrl, status_a, ctx->cs_mask, ctx->cs_mprefix, ctx->cs_cnt,
                                                  ctx->cs_mk[first], ctx->cs_mv[first], BITS, passes, ctx->hist_tot);   // hist_tot: 1024 key samples
     MPMK_LAUNCH_CHECK(ctx);
+    if (want_rank) mpmk_trace(ctx, s, 8);
     const uint32_t* m_dev = ctrl + CS_CTRL_MOVERS;
     constexpr int stage_bytes = 2 * MPMK_SORT_CHUNK * 4 + (512 / 32) * D * 4;   // staging + per-warp digit counters
+    constexpr int stage_bytes_lean = 2 * 2048 * 4 + (256 / 32) * D * 4;
     int in = first;
     const int mgrid = ntiles < ctx->sm_count ? ntiles : ctx->sm_count;   // persistent: CTAs loop over the movers' tiles
     for (int p = 0; p < passes; ++p) {
         const int o = 1 - in;
-        mpmk_launch(k_sort_onesweep<BITS, 512, 8>, dim3(mgrid), dim3(512), stage_bytes, s, ctx->cs_mk[in], ctx->cs_mv[in], ctx->cs_mk[o], ctx->cs_mv[o], 0, m_dev,
-                                                               p * BITS, ctx->sort_ctrl + OS_CTRL_HIST + p * 512,
-                                                               ctrl + OS_CTRL_STATUS + (size_t)p * ntiles * D, ctrl + p);
+        if (want_rank)   // beside the persistent p2g grid: 256 threads x 64 registers, 2048-key tiles (what p2g leaves free on an SM)
+            mpmk_launch(k_sort_onesweep<BITS, 256, 8>, dim3(mgrid), dim3(256), stage_bytes_lean, s, ctx->cs_mk[in], ctx->cs_mv[in], ctx->cs_mk[o], ctx->cs_mv[o], 0, m_dev,
+                                                                   p * BITS, ctx->sort_ctrl + OS_CTRL_HIST + p * 512,
+                                                                   ctrl + OS_CTRL_STATUS + (size_t)p * mtiles * D, ctrl + p);
+        else
+            mpmk_launch(k_sort_onesweep<BITS, 512, 8>, dim3(mgrid), dim3(512), stage_bytes, s, ctx->cs_mk[in], ctx->cs_mv[in], ctx->cs_mk[o], ctx->cs_mv[o], 0, m_dev,
+                                                                   p * BITS, ctx->sort_ctrl + OS_CTRL_HIST + p * 512,
+                                                                   ctrl + OS_CTRL_STATUS + (size_t)p * mtiles * D, ctrl + p);
         MPMK_LAUNCH_CHECK(ctx);
         in = o;
     }
+    if (want_rank) mpmk_trace(ctx, s, 9);
     // sorted movers are in buffer `in` (== 0); the other key buffer is free and receives x_t
     uint32_t* mx = ctx->cs_mk[1 - in];
     mpmk_launch(k_cs_place_movers, dim3(ctx->sm_count * 4), dim3(256), 0, s, ctx->cs_mk[in], ctx->cs_mv[in], ctrl, okeys, ctx->n, ctx->cs_mask, ctx->cs_mprefix,
                                                         ctx->cs_cnt, mx, ctx->keys_alt, ctx->perm, ctx->hist_tot, rank);
     MPMK_LAUNCH_CHECK(ctx);
+    if (want_rank) mpmk_trace(ctx, s, 10);
     mpmk_launch(k_cs_place_stayers, dim3(min(ntiles, ctx->sm_count * 4)), dim3(CS_THREADS), 0, s, keys, ctx->n, ctrl, status_b, ctx->cs_mask, ctx->cs_mprefix, ctx->cs_cnt, mx,
                                                      ctx->keys_alt, ctx->perm, rank);
     MPMK_LAUNCH_CHECK(ctx);
@@ -705,6 +714,8 @@ static int sort_init_bits(mpmk_ctx* ctx) {
     // configuration at a time, so everything on the side branch asks for the same (maximal) carve-out as p2g
     MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 256, 16>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 512, 8>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 256, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 2048 * 4 + (256 / 32) * D * 4));
+    MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_onesweep<BITS, 256, 8>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     MPMK_CHECK(ctx, cudaFuncSetAttribute(k_sort_digit_hist<BITS>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     return 0;
 }

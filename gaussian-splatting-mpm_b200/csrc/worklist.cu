@@ -271,7 +271,7 @@ __global__ void __launch_bounds__(256) k_lag_enter(float4* __restrict__ gin, flo
 
 // grid_in over block list [cur_list], zeroed beside g2p (which only reads grid_out) for the next substep's scatter.
 // (Zeroing it behind the grid pass, in k_grid, makes that kernel five times slower -- 12 -> 60 us on S-4M.)
-__global__ void __launch_bounds__(256) k_lag_clear_in(float4* __restrict__ gin, const uint32_t* __restrict__ list, const uint32_t* __restrict__ count,
+__global__ void __launch_bounds__(128) k_lag_clear_in(float4* __restrict__ gin, const uint32_t* __restrict__ list, const uint32_t* __restrict__ count,
                                                       int n, int nb) {
     const int64_t total = (int64_t)(*count) * 64;
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -286,7 +286,8 @@ __global__ void __launch_bounds__(256) k_lag_clear_in(float4* __restrict__ gin, 
 
 int mpmk_launch_lag_clear_in(mpmk_ctx* ctx, cudaStream_t s) {
     const int l = ctx->cur_list;
-    mpmk_launch(k_lag_clear_in, dim3(ctx->sm_count * 2), dim3(256), 0, s, (float4*)ctx->b.grid_in, ctx->block_list[l], ctx->block_count[l], ctx->n_grid, ctx->nb);
+    // (128 threads x 32 registers: fits beside five g2p CTAs)
+    mpmk_launch(k_lag_clear_in, dim3(ctx->sm_count * 4), dim3(128), 0, s, (float4*)ctx->b.grid_in, ctx->block_list[l], ctx->block_count[l], ctx->n_grid, ctx->nb);
     MPMK_LAUNCH_CHECK(ctx);
     return 0;
 }

@@ -59,7 +59,7 @@ def main():
         buf = (C.c_ulonglong * 16)()
         b.ctx.call("mpmk_debug_trace", C.cast(buf, C.c_void_p))
         t0 = buf[0]
-        trace = {k: round((buf[i] - t0) / 1e3, 1) for k, i in (("p2g_done", 1), ("grid_done", 2), ("g2p_done", 3), ("side_clear", 5), ("side_sort", 6), ("side_lists", 7))}
+        trace = {k: round((buf[i] - t0) / 1e3, 1) for k, i in (("p2g_done", 1), ("grid_done", 2), ("g2p_done", 3), ("side_clear", 5), ("side_flagscan", 8), ("side_radix", 9), ("side_movers", 10), ("side_sort", 6), ("side_lists", 7))}
     sops = sim._ops_at(sim.time)
     stages = ["sort", "prepare", "p2g", "grid", "g2p"]
     acc = {k: 0.0 for k in stages}

@@ -156,14 +156,14 @@ def test_udon_fixture_full_boundary_list(cuda_dev):
     e = _compare(g, o, dv_equiv=1e-4 * float(o.dx) / (36 * dt))
     # yield_stress hardened on the metal particles that yielded.  The cloud is sparse (2,153 particles on 100^3 nodes): most
     # particles only see their own scatter, their strain is rounding noise of a few ulp of 1.0, and with xi = 1 the hardened
-    # value is 2 mu (|eps_dev| + 1e-6) (constitutive_models.py:80-97): equal up to 5 ulp of log-strain, 1 % beyond that
+    # value is 2 mu (|eps_dev| + 1e-6) (constitutive_models.py:80-97): equal up to 8 ulp of log-strain, 5 % beyond that
     ys_g = g.mpm_model.yield_stress.to_torch().cpu().numpy()
     ys_o = o.in_original_order("yield_stress")
     assert (ys_o != np.float32(0.005)).mean() > 0.5
     # (the ~190 particles under the impulses / next to a neighbour strain for real, 1e-5 .. 1e-4: there the rounding of
     # the SVD factors, ~7e-7 absolute per return mapping, is up to a few percent of the strain sigma_y follows)
     err = np.abs(ys_g - ys_o)
-    bad = err > 2.0 * o.in_original_order("mu") * 6e-7 + 5e-2 * np.abs(ys_o)
+    bad = err > 2.0 * o.in_original_order("mu") * 1e-6 + 5e-2 * np.abs(ys_o)   # (1e-6: the offset the model itself adds to |eps_dev|)
     assert not bad.any(), (int(bad.sum()), list(zip(ys_g[bad][:8], ys_o[bad][:8])))
     big = ys_o > 1.0
     assert np.median(err[big] / ys_o[big]) < 1e-2
