@@ -173,7 +173,8 @@ def run_multi(a, rank, world, local, dev):
     # is only the checker), 64 k - 131 k particles, ids exact, x / cov within 1e-4.  A failure fails the bench.
     parity = None
     if not a.no_mg_parity:
-        from tests import mg_parity
+        sys.path.insert(0, os.path.join(ROOT, "tests"))   # by path: another package named `tests` may be importable on the box
+        import mg_parity
         parity = mg_parity.run_case("metal", 30, rank, world, dev, (0.0, 0.0, 20.0), ghost=2, migrate_every="auto", out=sys.stderr)
         if not parity["ok"]:
             if rank == 0:

@@ -114,9 +114,12 @@ extern "C" int mpmk_destroy(mpmk_ctx* ctx) {
     return 0;
 }
 
+// The captured batches no longer describe the context (particle count, bindings, slab, scalar parameters changed).
+// The executable graphs are kept, marked stale: the next capture of a batch of the same shape updates one of them in
+// place (cudaGraphExecUpdate: same topology, new kernel arguments) instead of instantiating a new one, which is what a
+// slab pays after every migration and a frame loop after every reload.
 void mpmk_drop_graphs(mpmk_ctx* ctx) {
-    for (int i = 0; i < ctx->n_graphs; ++i) cudaGraphExecDestroy(ctx->graphs[i].exec);
-    ctx->n_graphs = 0;
+    for (int i = 0; i < ctx->n_graphs; ++i) ctx->graphs[i].stale = true;
 }
 
 extern "C" int mpmk_bind(mpmk_ctx* ctx, const mpmk_bindings* b) {
@@ -285,6 +288,7 @@ static int lagged_substep(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, 
     MPMK_CHECK(ctx, cudaEventRecord(ctx->ev_join, side));
     // critical path
     if ((rc = mpmk_launch_p2g_lagged(ctx, dt, ops, s))) return rc;
+    if ((rc = mpmk_mg_halo_sum(ctx, s))) return rc;  // no-op unless a slab is set (mg.cu)
     TRACE(ctx, s, 1);
     MPMK_CHECK(ctx, cudaStreamWaitEvent(s, ctx->ev_clear, 0));
     if ((rc = mpmk_launch_grid_lagged(ctx, dt, ops, s))) return rc;
@@ -310,7 +314,10 @@ static int substeps_impl(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, i
     for (int i = 0; i < n_steps && rc == 0; ++i) {
         const bool last = (i == n_steps - 1);
         ctx->prm.flags = last ? user_flags : (user_flags & ~MPMK_WRITE_FTRIAL);
-        if (allow_lag && ctx->coherent && ctx->n > 0 && !ctx->mg.enabled && !(user_flags & MPMK_NO_LAG)) rc = lagged_substep(ctx, dt, ops, s);
+        // (slabs: the peer-memory halo is plain kernels and is captured like everything else; the NCCL halo path is issued
+        // eagerly and stays sequential)
+        if (allow_lag && ctx->coherent && ctx->n > 0 && (!ctx->mg.enabled || ctx->mg.peer) && !(user_flags & MPMK_NO_LAG))
+            rc = lagged_substep(ctx, dt, ops, s);
         else rc = substep_impl(ctx, dt, ops, s);
     }
     ctx->prm.flags = user_flags;
@@ -347,7 +354,7 @@ static int graph_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, 
     // look for a captured graph with identical launch parameters
     for (int i = 0; i < ctx->n_graphs; ++i) {
         mpmk_ctx::GraphEntry& g = ctx->graphs[i];
-        if (g.n_steps == n_steps && g.dt == dt && g.flags == user_flags && g.n == ctx->n && host_state_same(g.start, now) &&
+        if (!g.stale && g.n_steps == n_steps && g.dt == dt && g.flags == user_flags && g.n == ctx->n && host_state_same(g.start, now) &&
             memcmp(&g.ops, ops, sizeof(*ops)) == 0 && same_bindings(g.b, ctx->b)) {
             MPMK_CHECK(ctx, cudaGraphLaunch(g.exec, s));
             ctx->launches += g.kernels;
@@ -370,8 +377,17 @@ static int graph_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, 
     cudaGraph_t graph = nullptr;
     cudaError_t ce = cudaStreamEndCapture(cs, &graph);
     cudaGraphExec_t exec = nullptr;
+    int reused = -1;
     if (rc == 0 && ce == cudaSuccess) {
-        ce = cudaGraphInstantiate(&exec, graph, 0);
+        // a stale executable of the same shape (substeps, lagged or not from the start) takes the new arguments in place
+        for (int i = 0; i < ctx->n_graphs && reused < 0; ++i) {
+            mpmk_ctx::GraphEntry& g = ctx->graphs[i];
+            if (!g.stale || g.n_steps != n_steps || g.start.lag_ready != now.lag_ready || g.start.coherent != now.coherent) continue;
+            cudaGraphExecUpdateResultInfo info;
+            if (cudaGraphExecUpdate(g.exec, graph, &info) == cudaSuccess) { exec = g.exec; reused = i; }
+            else cudaGetLastError();   // topology differs (other op count, flags, merge vs full sort): instantiate below
+        }
+        if (reused < 0) ce = cudaGraphInstantiate(&exec, graph, 0);
     }
     if (graph) cudaGraphDestroy(graph);
     if (rc || ce != cudaSuccess) {
@@ -383,14 +399,21 @@ static int graph_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, 
         MPMK_CHECK(ctx, ce);
     }
     e.exec = exec;
+    e.stale = false;
+    e.kernels = ctx->launches - launches_before;   // kernels one replay executes
     host_state_get(ctx, &e.end);
-    if (ctx->n_graphs == MPMK_GRAPH_CACHE) {  // evict the oldest
-        cudaGraphExecDestroy(ctx->graphs[0].exec);
-        for (int i = 1; i < MPMK_GRAPH_CACHE; ++i) ctx->graphs[i - 1] = ctx->graphs[i];
-        ctx->n_graphs = MPMK_GRAPH_CACHE - 1;
+    if (reused >= 0) {
+        ctx->graphs[reused] = e;
+    } else {
+        if (ctx->n_graphs == MPMK_GRAPH_CACHE) {  // evict a stale entry if there is one, else the oldest
+            int victim = 0;
+            for (int i = 0; i < ctx->n_graphs; ++i) if (ctx->graphs[i].stale) { victim = i; break; }
+            cudaGraphExecDestroy(ctx->graphs[victim].exec);
+            for (int i = victim + 1; i < MPMK_GRAPH_CACHE; ++i) ctx->graphs[i - 1] = ctx->graphs[i];
+            ctx->n_graphs = MPMK_GRAPH_CACHE - 1;
+        }
+        ctx->graphs[ctx->n_graphs++] = e;
     }
-    ctx->graphs[ctx->n_graphs++] = e;
-    ctx->graphs[ctx->n_graphs - 1].kernels = ctx->launches - launches_before;   // kernels one replay executes
     MPMK_CHECK(ctx, cudaGraphLaunch(exec, s));
     ctx->ftrial_valid = (user_flags & MPMK_WRITE_FTRIAL) != 0;
     return 0;
@@ -435,6 +458,9 @@ extern "C" int mpmk_substeps(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* op
         rc = substeps_impl(ctx, dt, ops, 1, s, false);
         left -= 1;
     }
+    // (the classic -> lagged transition outside the graphs: every two-substep graph then starts from the same state)
+    if (rc == 0 && left >= 2 && lag_enabled() && !(user_flags & MPMK_NO_LAG) && ctx->coherent && ctx->n > 0 && !ctx->lag_ready)
+        rc = mpmk_launch_lag_enter(ctx, s);
     while (rc == 0 && left >= 2) {
         ctx->prm.flags = left == 2 ? user_flags : quiet;
         rc = graph_substeps(ctx, dt, ops, 2, s);

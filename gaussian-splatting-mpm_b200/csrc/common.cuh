@@ -127,6 +127,7 @@ struct mpmk_ctx {
     };
     struct GraphEntry {
         cudaGraphExec_t exec;
+        bool stale;               // arguments out of date: candidate for cudaGraphExecUpdate
         float dt;
         mpmk_substep_ops ops;
         int n_steps;

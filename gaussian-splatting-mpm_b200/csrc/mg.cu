@@ -119,6 +119,7 @@ extern "C" int mpmk_mg_set_slab(mpmk_ctx* ctx, int x_lo, int x_hi, int ghost, in
         MPMK_FAIL(ctx, MPMK_ERR_INVALID, "mpmk_mg_set_slab: receive buffers missing");
     m.recv_lo = recv_lo_dev; m.recv_hi = recv_hi_dev;
     m.enabled = m.world > 1;
+    ctx->lag_ready = false;
     mpmk_drop_graphs(ctx);   // captured substeps hold the old plane / row ranges
     return 0;
 }
@@ -130,6 +131,7 @@ extern "C" int mpmk_mg_set_count(mpmk_ctx* ctx, int64_t n) {
     if (n < 0 || n > ctx->capacity) MPMK_FAIL(ctx, MPMK_ERR_INVALID, "mpmk_mg_set_count: n=%lld capacity=%lld", (long long)n, (long long)ctx->capacity);
     ctx->n = n;
     ctx->coherent = false;
+    ctx->lag_ready = false;
     ctx->sorted_valid = false;
     ctx->prepared = false;
     mpmk_drop_graphs(ctx);

@@ -739,7 +739,11 @@ int mpmk_launch_sort_lagged(mpmk_ctx* ctx, cudaStream_t s) { return launch_sort_
 
 static int launch_sort_impl(mpmk_ctx* ctx, cudaStream_t s, bool want_rank) {
     if (ctx->n == 0) { ctx->sorted_valid = true; return 0; }
-    int passes = (ctx->key_bits + MPMK_MAX_RADIX_BITS - 1) / MPMK_MAX_RADIX_BITS;
+    // (a lagged batch sorts beside the persistent p2g grid, which leaves 16 K registers per SM: the 256-thread mover
+    // passes fit with digits of up to 8 bits -- 64 registers -- and not with 9 -- two digits per thread, 119 registers;
+    // a 512^3 grid's 27-bit keys then take four 7-bit passes instead of three 9-bit ones)
+    const int max_bits = want_rank ? 8 : MPMK_MAX_RADIX_BITS;
+    int passes = (ctx->key_bits + max_bits - 1) / max_bits;
     int bits = (ctx->key_bits + passes - 1) / passes;
     if (bits < 5) bits = 5;
     int rc;
