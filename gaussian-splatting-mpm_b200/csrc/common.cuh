@@ -43,6 +43,7 @@ struct MgState {
     bool enabled;
     int x_lo, x_hi, ghost;
     int y_lo, y_hi;          // row range the exchange / dense passes are restricted to
+    int z_lo, z_hi;          // ... and the window along the fastest axis (peer-memory path; mpmk_mg_set_window)
     int lo0, lo1, hi0, hi1;  // shared plane ranges with rank-1 / rank+1 (empty when lo1 == lo0)
     void* recv_lo;
     void* recv_hi;

@@ -69,15 +69,20 @@ __global__ void __launch_bounds__(256) k_grid(float4* __restrict__ gin, float4* 
     }
 }
 
-// multi-GPU: the same update, densely over the planes [x0, x1) shared with a neighbouring slab (mg.cu)
-__global__ void __launch_bounds__(256) k_grid_planes(float4* __restrict__ gin, float4* __restrict__ gout, int x0, int x1,
-                                                     int y0, int y1, int n, float dx, float dt, float gx, float gy, float gz,
+// multi-GPU: the same update, densely over the (up to two) plane ranges shared with the neighbouring slabs (mg.cu),
+// rows [y0, y1) x nodes [z0, z1)
+__global__ void __launch_bounds__(256) k_grid_planes(float4* __restrict__ gin, float4* __restrict__ gout, int xa0, int xa1, int xb0, int xb1,
+                                                     int y0, int y1, int z0, int z1, int n, float dx, float dt, float gx, float gy, float gz,
                                                      const GridOpsArg ops) {
-    const int64_t per_plane = (int64_t)(y1 - y0) * n, total = per_plane * (x1 - x0);
+    const int nz = z1 - z0;
+    const int64_t per_plane = (int64_t)(y1 - y0) * nz;
+    const int64_t ta = per_plane * (xa1 - xa0), total = ta + per_plane * (xb1 - xb0);
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int ix = x0 + (int)(i / per_plane);
-        const int64_t rem = i % per_plane;
-        const int iy = y0 + (int)(rem / n), iz = (int)(rem % n);
+        const bool second = i >= ta;
+        const int64_t j = second ? i - ta : i;
+        const int ix = (second ? xb0 : xa0) + (int)(j / per_plane);
+        const int64_t rem = j % per_plane;
+        const int iy = y0 + (int)(rem / nz), iz = z0 + (int)(rem % nz);
         // zeroes grid_in behind itself: the shared planes collect sums from the neighbours on nodes no local block list
         // knows about, so they are reset here, densely, instead of by a separate clear before the next scatter
         grid_node_update(gin, gout, ix, iy, iz, n, dx, dt, gx, gy, gz, ops, 1);
@@ -99,12 +104,12 @@ static int launch_grid(mpmk_ctx* ctx, float dt, const mpmk_substep_ops* ops, cud
     MPMK_LAUNCH_CHECK(ctx);
     if (ctx->mg.enabled) {
         const MgState& m = ctx->mg;
-        const int r0[2] = {m.lo0, m.hi0}, r1[2] = {m.lo1, m.hi1};
-        for (int k = 0; k < 2; ++k) {
-            if (r1[k] <= r0[k]) continue;
-            k_grid_planes<<<ctx->sm_count * 4, 256, 0, s>>>((float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out, r0[k], r1[k],
-                                                            m.y_lo, m.y_hi, ctx->n_grid, ctx->dx, dt, ctx->prm.gravity[0], ctx->prm.gravity[1],
-                                                            ctx->prm.gravity[2], a);
+        if (m.lo1 > m.lo0 || m.hi1 > m.hi0) {
+            // (the z window only narrows the peer-memory path; the NCCL path exchanges whole rows)
+            const int z0 = m.peer ? m.z_lo : 0, z1 = m.peer ? m.z_hi : ctx->n_grid;
+            k_grid_planes<<<ctx->sm_count * 4, 256, 0, s>>>((float4*)ctx->b.grid_in, (float4*)ctx->b.grid_out, m.lo0, m.lo1, m.hi0, m.hi1,
+                                                            m.y_lo, m.y_hi, z0, z1, ctx->n_grid, ctx->dx, dt, ctx->prm.gravity[0],
+                                                            ctx->prm.gravity[1], ctx->prm.gravity[2], a);
             MPMK_LAUNCH_CHECK(ctx);
         }
     }

@@ -111,6 +111,7 @@ extern "C" int mpmk_mg_set_slab(mpmk_ctx* ctx, int x_lo, int x_hi, int ghost, in
         MPMK_FAIL(ctx, MPMK_ERR_INVALID, "slab [%d,%d) too thin for ghost=%d (needs >= 2*ghost+2 planes)", x_lo, x_hi, ghost);
     if (y_lo < 0 || y_hi > n || y_hi <= y_lo) MPMK_FAIL(ctx, MPMK_ERR_INVALID, "bad y range [%d,%d)", y_lo, y_hi);
     m.x_lo = x_lo; m.x_hi = x_hi; m.ghost = ghost; m.y_lo = y_lo; m.y_hi = y_hi;
+    m.z_lo = 0; m.z_hi = n;   // until mpmk_mg_set_window narrows it
     // shared plane ranges, clamped to the grid; empty at the outer ranks
     m.lo0 = m.lo1 = m.hi0 = m.hi1 = 0;
     if (m.rank > 0) { m.lo0 = max(0, x_lo - ghost); m.lo1 = min(n, x_lo + ghost + 2); }
@@ -121,6 +122,18 @@ extern "C" int mpmk_mg_set_slab(mpmk_ctx* ctx, int x_lo, int x_hi, int ghost, in
     m.enabled = m.world > 1;
     ctx->lag_ready = false;
     mpmk_drop_graphs(ctx);   // captured substeps hold the old plane / row ranges
+    return 0;
+}
+
+// [z_lo, z_hi): nodes along the fastest axis that any rank's stencils can reach before the next migration (the same
+// on every rank, like the row range).  The peer-memory halo and the dense update of the shared planes are restricted
+// to rows x this window; the NCCL halo path keeps whole rows (contiguous runs) and ignores it.
+extern "C" int mpmk_mg_set_window(mpmk_ctx* ctx, int z_lo, int z_hi) {
+    if (!ctx) return MPMK_ERR_INVALID;
+    MgState& m = ctx->mg;
+    if (z_lo < 0 || z_hi > ctx->n_grid || z_hi <= z_lo) MPMK_FAIL(ctx, MPMK_ERR_INVALID, "bad z window [%d,%d)", z_lo, z_hi);
+    if (z_lo != m.z_lo || z_hi != m.z_hi) mpmk_drop_graphs(ctx);
+    m.z_lo = z_lo; m.z_hi = z_hi;
     return 0;
 }
 
@@ -178,47 +191,78 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
     return v;
 }
 
-// copy my partial sums of planes [x0, x0+nx) x rows [y0, y0+ny) into the neighbour's buffer of this epoch's parity,
-// then publish epoch+1 in the neighbour's flag
-__global__ void __launch_bounds__(256) k_halo_push(const float4* __restrict__ gin, float4* __restrict__ peer_buf, size_t buf_f4,
-                                                   uint32_t* peer_flag, uint32_t* my_ctrl, int done_word, int x0, int nx, int y0,
-                                                   int ny, int n) {
+#define MGP_ERR 6        // epoch at which a wait for a neighbour's push timed out (0 = never); read by the host at the next migration
+#define MGP_SPIN_NS 4000000000ull   // a neighbour that has not pushed after 4 s is dead or has skipped a substep
+
+__device__ __forceinline__ unsigned long long mg_now_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// bounded wait for a neighbour's flag to reach `want`: a rank that died or threw between substeps must not hang the
+// others inside a kernel (the host could not even reach mpmk_mg_peer_close).  On a timeout the error word is set, the
+// add proceeds on whatever the buffer holds, and every rank raises at its next migration (slabs.py).
+__device__ __forceinline__ void mg_wait_flag(const uint32_t* flag, uint32_t want, uint32_t* err) {
+    if (ld_acquire_sys(flag) >= want) return;
+    const unsigned long long t0 = mg_now_ns();
+    while (ld_acquire_sys(flag) < want) {
+        if (mg_now_ns() - t0 > MGP_SPIN_NS) { *err = want; return; }
+    }
+}
+
+// region of one side: planes [x0, x0+nx) x rows [y0, y0+ny) x nodes [z0, z0+nz); the exchange buffers are the dense
+// [nx][ny][nz] images of it
+struct MgRegion { int x0, nx; };
+
+// copy my partial sums of both shared regions into the neighbours' buffers of this epoch's parity (stores over NVLink),
+// then -- last block out -- publish epoch+1 in both neighbours' flags
+__global__ void __launch_bounds__(256) k_halo_push(const float4* __restrict__ gin, float4* __restrict__ peer_lo, float4* __restrict__ peer_hi,
+                                                   size_t buf_f4, uint32_t* flag_lo, uint32_t* flag_hi, uint32_t* my_ctrl, MgRegion lo,
+                                                   MgRegion hi, int y0, int ny, int z0, int nz, int n) {
     const uint32_t e = my_ctrl[MGP_EPOCH];
-    float4* dst = peer_buf + (size_t)(e & 1u) * buf_f4;
-    const int64_t per_plane = (int64_t)ny * n, total = per_plane * nx;
+    const size_t par = (size_t)(e & 1u) * buf_f4;
+    const int64_t per_plane = (int64_t)ny * nz;
+    const int64_t tlo = per_plane * lo.nx, total = tlo + per_plane * hi.nx;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t px = i / per_plane, rem = i - px * per_plane;
-        dst[i] = gin[((int64_t)(x0 + px) * n + y0) * n + rem];
+        const bool up = i >= tlo;
+        const int64_t j = up ? i - tlo : i;
+        const int64_t px = j / per_plane, rem = j - px * per_plane;
+        const int64_t py = rem / nz, pz = rem - py * nz;
+        const float4 v = gin[(((int64_t)((up ? hi.x0 : lo.x0) + px) * n + y0 + py) * n) + z0 + pz];
+        (up ? peer_hi : peer_lo)[par + j] = v;
     }
     __threadfence_system();
     __syncthreads();
-    if (threadIdx.x == 0 && atomicAdd(&my_ctrl[done_word], 1u) == gridDim.x - 1) {
-        my_ctrl[done_word] = 0u;
+    if (threadIdx.x == 0 && atomicAdd(&my_ctrl[MGP_DONE_LO], 1u) == gridDim.x - 1) {
+        my_ctrl[MGP_DONE_LO] = 0u;
         __threadfence_system();
-        st_release_sys(peer_flag, e + 1u);
+        if (lo.nx > 0) st_release_sys(flag_lo, e + 1u);
+        if (hi.nx > 0) st_release_sys(flag_hi, e + 1u);
     }
 }
 
 // wait for both neighbours' pushes of this epoch, add them (a + b here, b + a there: bit-identical sums), advance the epoch
 __global__ void __launch_bounds__(256) k_halo_wait_add(float4* __restrict__ gin, const float4* __restrict__ buf_lo,
                                                        const float4* __restrict__ buf_hi, size_t buf_f4, uint32_t* my_ctrl,
-                                                       int lo0, int nlo, int hi0, int nhi, int y0, int ny, int n) {
+                                                       MgRegion lo, MgRegion hi, int y0, int ny, int z0, int nz, int n) {
     const uint32_t e = my_ctrl[MGP_EPOCH];
     if (threadIdx.x == 0) {
-        if (nlo > 0) while (ld_acquire_sys(&my_ctrl[MGP_FLAG_LO]) < e + 1u) {}
-        if (nhi > 0) while (ld_acquire_sys(&my_ctrl[MGP_FLAG_HI]) < e + 1u) {}
+        if (lo.nx > 0) mg_wait_flag(&my_ctrl[MGP_FLAG_LO], e + 1u, &my_ctrl[MGP_ERR]);
+        if (hi.nx > 0) mg_wait_flag(&my_ctrl[MGP_FLAG_HI], e + 1u, &my_ctrl[MGP_ERR]);
     }
     __syncthreads();
-    const int64_t per_plane = (int64_t)ny * n;
-    const int64_t tlo = per_plane * nlo, total = tlo + per_plane * nhi;
+    const int64_t per_plane = (int64_t)ny * nz;
+    const int64_t tlo = per_plane * lo.nx, total = tlo + per_plane * hi.nx;
     const float4* blo = buf_lo + (size_t)(e & 1u) * buf_f4;
     const float4* bhi = buf_hi + (size_t)(e & 1u) * buf_f4;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const bool hi = i >= tlo;
-        const int64_t j = hi ? i - tlo : i;
+        const bool up = i >= tlo;
+        const int64_t j = up ? i - tlo : i;
         const int64_t px = j / per_plane, rem = j - px * per_plane;
-        float4* g = gin + (((int64_t)((hi ? hi0 : lo0) + px) * n + y0) * n + rem);
-        const float4 b = __ldcg((hi ? bhi : blo) + j);   // written by the peer: never through this SM's L1
+        const int64_t py = rem / nz, pz = rem - py * nz;
+        float4* g = gin + ((((int64_t)((up ? hi.x0 : lo.x0) + px) * n + y0 + py) * n) + z0 + pz);
+        const float4 b = __ldcg((up ? bhi : blo) + j);   // written by the peer: never through this SM's L1
         float4 a = *g;
         a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
         *g = a;
@@ -232,29 +276,33 @@ __global__ void __launch_bounds__(256) k_halo_wait_add(float4* __restrict__ gin,
 
 static int halo_sum_peer(mpmk_ctx* ctx, cudaStream_t s) {
     const MgState& m = ctx->mg;
-    const int n = ctx->n_grid, ny = m.y_hi - m.y_lo;
+    const int n = ctx->n_grid, ny = m.y_hi - m.y_lo, nz = m.z_hi - m.z_lo;
     const size_t buf_f4 = m.buf_bytes / 16;
-    if ((size_t)(2 * m.ghost + 2) * ny * n > buf_f4) MPMK_FAIL(ctx, MPMK_ERR_STATE, "peer exchange buffers too small for the shared region");
+    if ((size_t)(2 * m.ghost + 2) * ny * nz > buf_f4) MPMK_FAIL(ctx, MPMK_ERR_STATE, "peer exchange buffers too small for the shared region");
     uint32_t* my_ctrl = (uint32_t*)m.my_block;
     float4* gin = (float4*)ctx->b.grid_in;
+    const MgRegion lo = {m.lo0, m.lo1 - m.lo0}, hi = {m.hi0, m.hi1 - m.hi0};
     // my data for rank-1 lands in ITS side-1 buffers (I am its rank+1) and raises its FLAG_HI; for rank+1: side 0, FLAG_LO
-    if (m.lo1 > m.lo0) {
-        float4* pb = (float4*)(m.peer_block[0] + MGP_CTRL_BYTES + 2 * m.buf_bytes);
-        k_halo_push<<<ctx->sm_count * 2, 256, 0, s>>>(gin, pb, buf_f4, (uint32_t*)m.peer_block[0] + MGP_FLAG_HI, my_ctrl, MGP_DONE_LO,
-                                                     m.lo0, m.lo1 - m.lo0, m.y_lo, ny, n);
-        MPMK_LAUNCH_CHECK(ctx);
-    }
-    if (m.hi1 > m.hi0) {
-        float4* pb = (float4*)(m.peer_block[1] + MGP_CTRL_BYTES);
-        k_halo_push<<<ctx->sm_count * 2, 256, 0, s>>>(gin, pb, buf_f4, (uint32_t*)m.peer_block[1] + MGP_FLAG_LO, my_ctrl, MGP_DONE_HI,
-                                                     m.hi0, m.hi1 - m.hi0, m.y_lo, ny, n);
-        MPMK_LAUNCH_CHECK(ctx);
-    }
+    float4* pb_lo = lo.nx > 0 ? (float4*)(m.peer_block[0] + MGP_CTRL_BYTES + 2 * m.buf_bytes) : nullptr;
+    float4* pb_hi = hi.nx > 0 ? (float4*)(m.peer_block[1] + MGP_CTRL_BYTES) : nullptr;
+    uint32_t* fl_lo = lo.nx > 0 ? (uint32_t*)m.peer_block[0] + MGP_FLAG_HI : nullptr;
+    uint32_t* fl_hi = hi.nx > 0 ? (uint32_t*)m.peer_block[1] + MGP_FLAG_LO : nullptr;
+    k_halo_push<<<ctx->sm_count * 2, 256, 0, s>>>(gin, pb_lo, pb_hi, buf_f4, fl_lo, fl_hi, my_ctrl, lo, hi, m.y_lo, ny, m.z_lo, nz, n);
+    MPMK_LAUNCH_CHECK(ctx);
     const float4* my_lo = (const float4*)(m.my_block + MGP_CTRL_BYTES);
     const float4* my_hi = (const float4*)(m.my_block + MGP_CTRL_BYTES + 2 * m.buf_bytes);
-    k_halo_wait_add<<<ctx->sm_count * 2, 256, 0, s>>>(gin, my_lo, my_hi, buf_f4, my_ctrl, m.lo0, m.lo1 - m.lo0, m.hi0, m.hi1 - m.hi0,
-                                                     m.y_lo, ny, n);
+    k_halo_wait_add<<<ctx->sm_count * 2, 256, 0, s>>>(gin, my_lo, my_hi, buf_f4, my_ctrl, lo, hi, m.y_lo, ny, m.z_lo, nz, n);
     MPMK_LAUNCH_CHECK(ctx);
+    return 0;
+}
+
+// epoch at which this rank gave up waiting for a neighbour's halo push (0: never).  Synchronises `stream`.
+extern "C" int mpmk_mg_peer_error(mpmk_ctx* ctx, uint32_t* epoch_out, void* stream) {
+    if (!ctx || !epoch_out) return MPMK_ERR_INVALID;
+    *epoch_out = 0;
+    if (!ctx->mg.peer || !ctx->mg.my_block) return 0;
+    MPMK_CHECK(ctx, cudaMemcpyAsync(epoch_out, (uint32_t*)ctx->mg.my_block + MGP_ERR, 4, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    MPMK_CHECK(ctx, cudaStreamSynchronize((cudaStream_t)stream));
     return 0;
 }
 
@@ -349,15 +397,17 @@ extern "C" int mpmk_mg_halo_exchange(mpmk_ctx* ctx, void* stream) {
 }
 
 // ---- migration helpers (the protocol itself is mpm_solver/slabs.py) ------------------------------------------
-// stats layout (int32[8]): {leavers down, leavers up, beyond ghost, -min row, max row, max(|v_x|,|v_y|) (float bits), 0, 0}
+// stats layout (int32[12]): {leavers down, leavers up, beyond ghost, -min row, max row, max(|v_x|,|v_y|,|v_z|) (float bits),
+//                            -min z, max z, halo timeout epoch (peer path), 0, 0, 0}
 struct MgRecordPtrs {
     const float4* src[16];
     float4* dst[16];
     int n_arrays;
 };
 
-__global__ void k_mg_stats_init(int* stats, int n_grid) {
-    if (threadIdx.x < 8) stats[threadIdx.x] = (threadIdx.x == 3) ? -n_grid : (threadIdx.x == 4 ? -1 : 0);
+__global__ void k_mg_stats_init(int* stats, int n_grid, const uint32_t* ctrl) {
+    const int t = threadIdx.x;
+    if (t < 12) stats[t] = (t == 3 || t == 6) ? -n_grid : ((t == 4 || t == 7) ? -1 : (t == 8 && ctrl ? (int)ctrl[MGP_ERR] : 0));
 }
 
 __global__ void __launch_bounds__(256) k_mg_scan(const uint32_t* __restrict__ keys, const float4* __restrict__ vv, int64_t n, int nt,
@@ -365,7 +415,7 @@ __global__ void __launch_bounds__(256) k_mg_scan(const uint32_t* __restrict__ ke
                                                  int* __restrict__ idx_lo, int* __restrict__ idx_hi) {
     const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned lane = threadIdx.x & 31;
-    int by = -1, nby = -(1 << 30), far = 0;
+    int by = -1, nby = -(1 << 30), bz = -1, nbz = -(1 << 30), far = 0;
     float av = 0.f;
     bool lo = false, hi = false;
     if (p < n) {
@@ -374,10 +424,12 @@ __global__ void __launch_bounds__(256) k_mg_scan(const uint32_t* __restrict__ ke
         const int bx = (int)(tile / (uint32_t)(nt * nt)) * 4 + (int)((k >> 4) & 3u);
         by = (int)((tile / (uint32_t)nt) % (uint32_t)nt) * 4 + (int)((k >> 2) & 3u);
         nby = -by;
+        bz = (int)(tile % (uint32_t)nt) * 4 + (int)(k & 3u);
+        nbz = -bz;
         lo = bx < x_lo; hi = bx >= x_hi;
         far = (bx < x_lo - ghost || bx >= x_hi + ghost) ? 1 : 0;
         const float4 v = vv[p];
-        av = fmaxf(fabsf(v.x), fabsf(v.y));   // drift along the slab axis and along the rows of the exchange window
+        av = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fabsf(v.z));   // drift along the slab axis and inside the exchange window
     }
     // leavers: one atomic per warp and direction, order inside the lists is irrelevant
     const unsigned mlo = __ballot_sync(0xffffffffu, lo), mhi = __ballot_sync(0xffffffffu, hi);
@@ -396,12 +448,16 @@ __global__ void __launch_bounds__(256) k_mg_scan(const uint32_t* __restrict__ ke
     far = __reduce_add_sync(0xffffffffu, far);
     nby = __reduce_max_sync(0xffffffffu, nby);
     by = __reduce_max_sync(0xffffffffu, by);
+    nbz = __reduce_max_sync(0xffffffffu, nbz);
+    bz = __reduce_max_sync(0xffffffffu, bz);
     int avb = __reduce_max_sync(0xffffffffu, __float_as_int(av));   // non-negative floats order like their bits
     if (lane == 0) {
         if (far) atomicAdd(&stats[2], far);
         atomicMax(&stats[3], nby);
         atomicMax(&stats[4], by);
         atomicMax(&stats[5], avb);
+        atomicMax(&stats[6], nbz);
+        atomicMax(&stats[7], bz);
     }
 }
 
@@ -483,7 +539,7 @@ extern "C" int mpmk_mg_scan(mpmk_ctx* ctx, void* stats_dev, void* idx_lo_dev, vo
     REQUIRE_SLAB(ctx);
     cudaStream_t s = (cudaStream_t)stream;
     const MgState& m = ctx->mg;
-    k_mg_stats_init<<<1, 32, 0, s>>>((int*)stats_dev, ctx->n_grid);
+    k_mg_stats_init<<<1, 32, 0, s>>>((int*)stats_dev, ctx->n_grid, (m.peer && m.my_block) ? (const uint32_t*)m.my_block : nullptr);
     MPMK_LAUNCH_CHECK(ctx);
     if (ctx->n > 0) {
         k_mg_scan<<<div_up(ctx->n, 256), 256, 0, s>>>((const uint32_t*)ctx->b.keys, (const float4*)ctx->b.set[ctx->cur].vv, ctx->n,

@@ -125,6 +125,8 @@ def lib():
         "mpmk_mg_init": (i, [vp, C.c_char_p, vp, i, i, i]),
         "mpmk_mg_finalize": (i, [vp]),
         "mpmk_mg_set_slab": (i, [vp, i, i, i, i, i, vp, vp]),
+        "mpmk_mg_set_window": (i, [vp, i, i]),
+        "mpmk_mg_peer_error": (i, [vp, C.POINTER(C.c_uint32), vp]),
         "mpmk_mg_halo_exchange": (i, [vp, vp]),
         "mpmk_mg_peer_alloc": (i, [vp, i64, vp, i]),
         "mpmk_mg_peer_open": (i, [vp, vp, vp]),

@@ -132,6 +132,10 @@ def unpack_records(store: dict, idx: torch.Tensor, rows: torch.Tensor):
 
 
 # ---- migration ----------------------------------------------------------------------------------
+def _base_z_i32(keys: torch.Tensor, nt: int):
+    return ((keys >> 6) % nt) * 4 + (keys & 3)
+
+
 def _base_xy_i32(keys: torch.Tensor, nt: int):
     """(bx, by) of int32 keys without widening (one pass over 4 B per particle)"""
     tile = keys >> 6
@@ -158,6 +162,9 @@ def _payload_exchange(send_lo, send_hi, n_from_lo, n_from_hi, rank, world, group
     return recv_lo, recv_hi
 
 
+SCAN_WIDTH = 9   # integers every rank contributes to the migration's one all_gather (TorchRecordOps.scan)
+
+
 class TorchRecordOps:
     """scan / pack / refill on plain torch tensors of any device (the CPU tests run this over gloo)"""
 
@@ -166,16 +173,19 @@ class TorchRecordOps:
         self.device = store["keys"].device
 
     def scan(self, n, x_lo, x_hi, ghost):
-        """int64[6] on the device: leavers down, leavers up, beyond ghost, -min row, max row, max(|vx|,|vy|) bits"""
+        """int64[SCAN_WIDTH] on the device: leavers down, leavers up, beyond ghost, -min row, max row, max |v| component
+        (float bits), -min z, max z, halo timeout epoch (0 here: no peer-memory halo without the library)"""
         if n == 0:
             self.lo_mask = self.hi_mask = torch.zeros(0, dtype=torch.bool, device=self.device)
-            return torch.tensor([0, 0, 0, -self.n_grid, -1, 0], dtype=torch.int64, device=self.device)
+            return torch.tensor([0, 0, 0, -self.n_grid, -1, 0, -self.n_grid, -1, 0], dtype=torch.int64, device=self.device)
         bx, by = _base_xy_i32(self.store["keys"][:n], self.nt)
+        bz = _base_z_i32(self.store["keys"][:n], self.nt)
         self.lo_mask, self.hi_mask = bx < x_lo, bx >= x_hi
         far = (bx < x_lo - ghost) | (bx >= x_hi + ghost)
-        vmax = self.store["vv"][:n, :2].abs().max().reshape(1).to(torch.float32).view(torch.int32)[0]
+        vmax = self.store["vv"][:n, :3].abs().max().reshape(1).to(torch.float32).view(torch.int32)[0]
+        zero = torch.zeros((), dtype=torch.int64, device=self.device)
         return torch.stack([self.lo_mask.sum(), self.hi_mask.sum(), far.sum(), -by.min().to(torch.int64),
-                            by.max().to(torch.int64), vmax.to(torch.int64)])
+                            by.max().to(torch.int64), vmax.to(torch.int64), -bz.min().to(torch.int64), bz.max().to(torch.int64), zero])
 
     def pack_leavers(self, n_lo, n_hi):
         self.idx_lo = torch.nonzero_static(self.lo_mask, size=n_lo).flatten()
@@ -210,13 +220,13 @@ class CudaRecordOps:
         self.b, self._stream = backend, stream_fn
         dev = backend.device
         self.device = dev
-        self.stats = torch.zeros(8, dtype=torch.int32, device=dev)
+        self.stats = torch.zeros(12, dtype=torch.int32, device=dev)
         self.idx_lo = torch.zeros(backend.capacity, dtype=torch.int32, device=dev)
         self.idx_hi = torch.zeros(backend.capacity, dtype=torch.int32, device=dev)
 
     def scan(self, n, x_lo, x_hi, ghost):
         self.b.ctx.call("mpmk_mg_scan", self.stats.data_ptr(), self.idx_lo.data_ptr(), self.idx_hi.data_ptr(), self._stream())
-        return self.stats[:6].to(torch.int64)
+        return self.stats[:SCAN_WIDTH].to(torch.int64)
 
     def pack_leavers(self, n_lo, n_hi):
         self.n_lo, self.n_hi = n_lo, n_hi
@@ -265,14 +275,18 @@ def migrate(store: dict, n: int, capacity: int, bounds, rank: int, ghost: int, n
         ops = TorchRecordOps(store, nt, n_grid)
     _mark("begin", device)
     mine = ops.scan(n, x_lo, x_hi, ghost)
-    table = torch.empty(world * 6, dtype=torch.int64, device=device)
+    table = torch.empty(world * SCAN_WIDTH, dtype=torch.int64, device=device)
     if world > 1:
         dist.all_gather_into_tensor(table, mine.contiguous(), group=group)
     else:
-        table[:6] = mine
+        table[:SCAN_WIDTH] = mine
     _mark("scan", device)
-    table = table.view(world, 6).cpu()                    # the one synchronisation
+    table = table.view(world, SCAN_WIDTH).cpu()           # the one synchronisation
     _mark("allgather+sync", device)
+    if int(table[:, 8].max()):     # collective: every rank sees the same table, every rank raises
+        bad = [r for r in range(world) if int(table[r, 8])]
+        raise SlabError(f"ranks {bad}: a neighbour's halo push did not arrive within the spin budget (substep epochs "
+                        f"{[int(table[r, 8]) for r in bad]}): a rank died or skipped a substep; the grid sums since then are invalid")
     if int(table[:, 2].sum()):
         bad = [r for r in range(world) if int(table[r, 2])]
         raise SlabError(f"ranks {bad}: particles drifted more than ghost={ghost} planes outside their slab between "
@@ -282,8 +296,10 @@ def migrate(store: dict, n: int, capacity: int, bounds, rank: int, ghost: int, n
     n_from_hi = int(table[rank + 1, 0]) if rank < world - 1 else 0
     y_min, y_max = -int(table[:, 3].max()), int(table[:, 4].max())
     rows = (0, n_grid) if y_max < y_min else (max(0, y_min - ghost - 1), min(n_grid, y_max + 3 + ghost + 1))
+    z_min, z_max = -int(table[:, 6].max()), int(table[:, 7].max())
+    zs = (0, n_grid) if z_max < z_min else (max(0, z_min - ghost - 1), min(n_grid, z_max + 3 + ghost + 1))
     vmax = float(table[:, 5].max().to(torch.int32).reshape(1).view(torch.float32)[0])
-    stats = {"sent_lo": n_lo, "sent_hi": n_hi, "recv_lo": n_from_lo, "recv_hi": n_from_hi, "rows": rows, "vmax": vmax}
+    stats = {"sent_lo": n_lo, "sent_hi": n_hi, "recv_lo": n_from_lo, "recv_hi": n_from_hi, "rows": rows, "zs": zs, "vmax": vmax}
     if n_lo + n_hi + n_from_lo + n_from_hi == 0:
         return n, stats
     n_new = n - n_lo - n_hi + n_from_lo + n_from_hi
@@ -298,11 +314,12 @@ def migrate(store: dict, n: int, capacity: int, bounds, rank: int, ghost: int, n
     return n_new, stats
 
 
-def global_row_range(store: dict, n: int, nt: int, n_grid: int, margin: int, group=None):
-    """[y_lo, y_hi): rows of the shared planes any rank's stencils can reach before the next migration"""
+def global_row_range(store: dict, n: int, nt: int, n_grid: int, margin: int, group=None, axis="y"):
+    """[y_lo, y_hi): rows of the shared planes any rank's stencils can reach before the next migration (axis="z": the
+    same along the fastest axis)"""
     device = store["keys"].device
     if n > 0:
-        _, by = _base_xy_i32(store["keys"][:n], nt)
+        by = _base_xy_i32(store["keys"][:n], nt)[1] if axis == "y" else _base_z_i32(store["keys"][:n], nt)
         lo, hi = by.min().to(torch.int64), by.max().to(torch.int64)
     else:
         lo = torch.tensor(n_grid, dtype=torch.int64, device=device)
@@ -454,13 +471,15 @@ class SlabSimulator:
         of its own ids (zeros elsewhere), the sum makes the table complete on all ranks"""
         dist.all_reduce(self.backend.init_cov, group=self.group)
 
-    def _set_slab(self, rows=None):
+    def _set_slab(self, rows=None, zs=None):
         b = self.backend
         y_lo, y_hi = rows if rows is not None else global_row_range(self._store(), b.n, self.nt, self.n_grid, self.ghost + 1, self.group)
-        self.rows = (y_lo, y_hi)
+        z_lo, z_hi = zs if zs is not None else global_row_range(self._store(), b.n, self.nt, self.n_grid, self.ghost + 1, self.group, axis="z")
+        self.rows, self.zs = (y_lo, y_hi), (z_lo, z_hi)
         b.ctx.call("mpmk_mg_set_slab", self.bounds[self.rank], self.bounds[self.rank + 1], self.ghost, y_lo, y_hi,
                    self._recv_lo.data_ptr() if self._recv_lo is not None else None,
                    self._recv_hi.data_ptr() if self._recv_hi is not None else None)
+        b.ctx.call("mpmk_mg_set_window", z_lo, z_hi)
 
     def migrate(self):
         b = self.backend
@@ -476,7 +495,7 @@ class SlabSimulator:
         self.stats["received"] += st["recv_lo"] + st["recv_hi"]
         self._since_migration = 0
         self._choose_interval(st["vmax"])
-        self._set_slab(st["rows"])
+        self._set_slab(st["rows"], st["zs"])
         _mark("set_slab", self.device)
         return st
 

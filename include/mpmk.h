@@ -234,13 +234,21 @@ MPMK_API int mpmk_mg_finalize(mpmk_ctx* ctx);
  * outer ranks); from here on mpmk_substep/mpmk_substeps include the halo sum      */
 MPMK_API int mpmk_mg_set_slab(mpmk_ctx* ctx, int x_lo, int x_hi, int ghost, int y_lo, int y_hi, void* recv_lo_dev,
                               void* recv_hi_dev);
+/* [z_lo, z_hi): the nodes along the fastest grid axis any rank's stencils can reach before the next migration (same
+ * on every rank).  Narrows the peer-memory halo and the dense update of the shared planes to rows x this window (the
+ * NCCL halo path keeps whole rows).  mpmk_mg_set_slab resets it to [0, n_grid).                       */
+MPMK_API int mpmk_mg_set_window(mpmk_ctx* ctx, int z_lo, int z_hi);
+/* peer-memory halo: substep epoch at which this rank gave up waiting (4 s) for a neighbour's push; 0 = never.
+ * Synchronises `stream`.  mpmk_mg_scan also reports it in stats[8], which is how slabs.py raises on every rank. */
+MPMK_API int mpmk_mg_peer_error(mpmk_ctx* ctx, uint32_t* epoch_out, void* stream);
 /* new live particle count after a host-side migration (mpm_solver/slabs.py); unlike mpmk_set_count
  * it keeps the current set and the validity of the stored F_trial records                       */
 MPMK_API int mpmk_mg_set_count(mpmk_ctx* ctx, int64_t n_particles);
 /* Migration helpers; the protocol is mpm_solver/slabs.py.  A record = the 16-byte entries of the 12 set arrays
  * and ft0..ft2 (15 x 4 words) + the key = 61 x int32.
- * scan: one pass over the live keys; stats_dev int32[8] = {leavers to rank-1, leavers to rank+1, particles more
- * than `ghost` planes outside the slab, -(min base row), max base row, max(|v_x|,|v_y|) (float bits), 0, 0};
+ * scan: one pass over the live keys; stats_dev int32[12] = {leavers to rank-1, leavers to rank+1, particles more
+ * than `ghost` planes outside the slab, -(min base row), max base row, max |v| component (float bits), -(min base z),
+ * max base z, halo timeout epoch (peer path, else 0), 0, 0, 0};
  * idx_lo_dev / idx_hi_dev int32[capacity] receive the slots of the leavers (unordered).                      */
 MPMK_API int mpmk_mg_scan(mpmk_ctx* ctx, void* stats_dev, void* idx_lo_dev, void* idx_hi_dev, void* stream);
 /* rows_dev int32[count][61] <- records at slots idx_dev[0..count)                                          */
