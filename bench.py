@@ -290,6 +290,19 @@ def run_multi(a, rank, world, local, dev):
     ke = max(5, min(a.steps, 10))
     e2e_ms = timed(lambda: e2e_frames(ke), 1)
     assert bool(torch.isfinite(out_xyz).all())
+    if os.environ.get("MPMK_SLAB_TIMING"):   # where a frame's time goes (synchronising between the phases; not the timed run)
+        import collections
+        ph = collections.OrderedDict()
+        def lap(name, fn):
+            torch.cuda.synchronize(); dist.barrier(); t_ = time.time(); fn(); torch.cuda.synchronize(); ph[name] = ph.get(name, 0.0) + (time.time() - t_) * 1e3
+        for _ in range(3):
+            lap("h2d", lambda: [stage[0][k].copy_(pin[k], non_blocking=True) for k in stage[0]])
+            lap("reload", lambda: sl.reload(stage[0]["xyz"], stage[0]["cov"], stage[0]["vol"], stage[0]["vel"], ids))
+            lap("step", lambda: sl.step(S, dt))
+            lap("export", lambda: b.export(want_R=True))
+            lap("d2h", lambda: (out_xyz.copy_(b.out_xyz[rank * n0:(rank + 1) * n0], non_blocking=True), out_cov.copy_(b.out_cov[rank * n0:(rank + 1) * n0], non_blocking=True)))
+        if rank == 0:
+            print("frame phases, ms (3 frames, serialised):", {k: round(v / 3, 2) for k, v in ph.items()}, file=sys.stderr, flush=True)
     peak, peak_src = _peaks()
     sub_bytes = 216.0 * N + 72.0 * float(touched.item())
     allin_ms = ms / (a.steps * S)

@@ -197,6 +197,10 @@ struct __align__(16) G2PWarpSmem {
     float4 tile[MPMK_TILE_NODES];
     uint32_t perm[2][32];  // permutation (LAG: rank) entries of batches B/C (ring), kept out of registers
     uint32_t key[3][32];   // keys of batches A/B/C (ring)
+#ifdef G2P_TILE_BULK
+    uint64_t bar;          // mbarrier of the tile's bulk copies
+    uint64_t pad_;
+#endif
 };
 
 template <bool LAG>
@@ -208,6 +212,12 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
     G2PWarpSmem& S = reinterpret_cast<G2PWarpSmem*>(g2p_smem_raw)[warp];
     const int n = a.n_grid;
 
+#ifdef G2P_TILE_BULK
+    if (lane == 0) mbar_init(&S.bar, 1);
+    unsigned tile_parity = 0;
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncwarp();
+#endif
     BatchStream bs;
     bs.init();
     const uint32_t n_items = a.cnt->n_items;
@@ -240,6 +250,21 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
         cp_async_wait<0>();
         __syncwarp();
         const int tz = dA.tile % a.nt, ty = (dA.tile / a.nt) % a.nt, tx = dA.tile / (a.nt * a.nt);
+#ifdef G2P_TILE_BULK
+        // the tile as 36 bulk copies (TMA engine, 1-D): one 96-byte row of 6 nodes each, completion on the warp's mbarrier.
+        // Tiles that stick out of the grid keep the per-node path.
+        const bool bulk_tile = dA.first && (4 * tx + 6 <= n) && (4 * ty + 6 <= n) && (4 * tz + 6 <= n);
+        if (bulk_tile) {
+            fence_proxy_async_smem();   // the previous item's gathers (generic proxy) read what the copies overwrite
+            __syncwarp();
+            if (lane == 0) mbar_expect_tx(&S.bar, MPMK_TILE_NODES * 16);
+            __syncwarp();
+            for (int r = lane; r < 36; r += 32) {
+                const int gx = 4 * tx + r / 6, gy = 4 * ty + r % 6;
+                bulk_g2s(&S.tile[r * 6], a.grid_out + (((size_t)gx * n + gy) * n + 4 * tz), 96, &S.bar);
+            }
+        } else
+#endif
         if (dA.first) {
             // a new item: restage the node tile (the previous item's gathers ended with __syncwarp)
             for (int i = lane; i < MPMK_TILE_NODES; i += 32) {
@@ -267,6 +292,9 @@ __global__ void __launch_bounds__(G2P_WARPS * 32, G2P_MIN_CTAS) k_g2p(const G2PA
         }
         cp_async_commit();
         cp_async_wait<1>();  // the tile has landed; batch B's records / batch C's entries stay in flight
+#ifdef G2P_TILE_BULK
+        if (bulk_tile) { mbar_wait(&S.bar, tile_parity); tile_parity ^= 1u; }
+#endif
         __syncwarp();
 
         if (lane < dA.count) {

@@ -260,6 +260,22 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
             if (dB.count == 0 || dB.first) {
                 if (cur_cell >= 0 && node_lane) p2g_flush_run<LAG>(a, S.tile, cur_cell, noff, ni, nj, nk, acc, acc2, stamp);
                 __syncwarp();
+#ifdef P2G_FLUSH_BULK
+                // the tile as 36 bulk reductions (TMA engine, cp.reduce.async.bulk .add.f32): one 96-byte row of 6 nodes each.
+                // Tiles that stick out of the grid keep the per-node path.
+                if ((4 * tx + 6 <= n) && (4 * ty + 6 <= n) && (4 * tz + 6 <= n)) {
+                    fence_proxy_async_smem();   // the tile was written through the generic proxy
+                    __syncwarp();
+                    for (int r = lane; r < 36; r += 32) {
+                        const int gx = 4 * tx + r / 6, gy = 4 * ty + r % 6;
+                        bulk_red_add_f32(a.grid_in + (((size_t)gx * n + gy) * n + 4 * tz), &S.tile[(r / 6) * P2G_TILE_SX + (r % 6) * 6], 96);
+                    }
+                    bulk_commit();
+                    bulk_wait_read0();          // the engine has read the rows: the tile may be reset
+                    __syncwarp();
+                    for (int i = lane; i < P2G_TILE_F4; i += 32) S.tile[i] = zero4;
+                } else
+#endif
                 for (int i = lane; i < MPMK_TILE_NODES; i += 32) {
                     const int ti = i + i / 36;  // x*37 + y*6 + z
                     const float4 t = S.tile[ti];
