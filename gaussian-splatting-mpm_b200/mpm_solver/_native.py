@@ -121,6 +121,18 @@ def lib():
         "mpmk_export": (i, [vp, vp, vp, vp, vp, vp]),
         "mpmk_export_world": (i, [vp, vp, C.POINTER(WorldXform), vp, vp, vp]),
         "mpmk_read_counters": (i, [vp, C.POINTER(Counters), vp]),
+        "mpmk_opt_stress": (i, [vp, i64, vp, vp, vp, vp, vp]),
+        "mpmk_opt_stress_grad": (i, [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp]),
+        "mpmk_opt_p2g": (i, [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, f, vp]),
+        "mpmk_opt_p2g_grad": (i, [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, f, vp]),
+        "mpmk_opt_grid": (i, [vp, vp, vp, vp, f, vp, vp, vp, vp]),
+        "mpmk_opt_grid_grad": (i, [vp, vp, vp, vp, vp, vp, vp]),
+        "mpmk_opt_g2p": (i, [vp, i64, vp, vp, vp, vp, vp, vp, vp, f, vp]),
+        "mpmk_opt_g2p_grad": (i, [vp, i64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, f, vp]),
+        "mpmk_opt_cov": (i, [vp, i64, vp, vp, vp, vp]),
+        "mpmk_opt_cov_grad": (i, [vp, i64, vp, vp, vp, vp, vp]),
+        "mpmk_opt_mu_lam_grad": (i, [vp, i64, vp, vp, vp, vp, vp, vp, vp]),
+        "mpmk_opt_learn": (i, [vp, i64, vp, vp, vp, vp, vp]),
         "mpmk_launch_count": (i64, [vp]),
         "mpmk_mg_init": (i, [vp, C.c_char_p, vp, i, i, i]),
         "mpmk_mg_finalize": (i, [vp]),

@@ -571,6 +571,90 @@ class MPM_state:
         F.fill([1.0, 0.0, 0.0, 0.0, 1.0, 0.0, 0.0, 0.0, 1.0])
 
 
+
+class MPM_state:
+    """Particle + grid state (reference: model.py:77-132)."""
+
+    def __init__(self, n_particles, xyzs, covs, volumes, args, _backend: _Backend = None):
+        self.n_particles = n_particles
+        if _backend is None:
+            raise _native.MpmkError("MPM_state is constructed by MPM_Simulator (it shares the packed backend with MPM_model)")
+        self._backend = b = _backend
+        dev = b.device
+        n = b.n
+        F = [("f0", 0), ("f0", 1), ("f0", 2), ("f0", 3), ("f1", 0), ("f1", 1), ("f1", 2), ("f1", 3), ("f2", 0)]
+        Cc = [("c0", 0), ("c0", 1), ("c0", 2), ("c0", 3), ("c1", 0), ("c1", 1), ("c1", 2), ("c1", 3), ("cs", 0)]
+        S6 = [("cs", 1), ("cs", 2), ("cs", 3), ("s1", 0), ("s1", 1), ("s1", 2)]
+        CV = [("cv0", 0), ("cv0", 1), ("cv0", 2), ("cv0", 3), ("cv1", 0), ("cv1", 1)]
+        inval = b.invalidate
+        self.particle_vol = _VolField(b, [("s1", 3)], (), after_write=inval)
+        self.particle_density = PlainField(torch.full((max(n, 1),), float(args.density), dtype=torch.float32, device=dev))
+        self.particle_mass = FieldView(b, [("xm", 3)], (), after_write=inval)
+        self._xyz_packed = FieldView(b, [("xm", 0), ("xm", 1), ("xm", 2)], (3,), after_write=b.recompute_keys)
+        self.particle_xyz = _ExportField(b, "xyz", self._xyz_packed)
+        self.particle_vel = FieldView(b, [("vv", 0), ("vv", 1), ("vv", 2)], (3,), after_write=inval)
+        self.particle_F = FieldView(b, F, (3, 3), after_write=lambda: b.mark_stress_dirty(f_written=True))
+        # (the reference overwrites particle_stress from F_trial at the start of every p2g2p, utils.py:14-54)
+        self.particle_stress = _SymStressField(b, S6, (3, 3), after_write=b.mark_stress_dirty)
+        self.particle_C = FieldView(b, Cc, (3, 3), after_write=inval)
+        self.particle_pressure = PlainField(torch.zeros(max(n, 1), dtype=torch.float32, device=dev))
+        self.particle_init_cov = PlainField(b.init_cov.view(-1), after_write=inval)
+        self._cov_packed = FieldView(b, CV, (6,), after_write=inval)
+        self.particle_cov = _ExportField(b, "cov", self._cov_packed)
+        self.particle_R = _ExportField(b, "R", None)
+        self.particle_F_trial = _FTrialField(b, F)
+
+        # initialisation, model.py:101-115
+        self._args_density = float(args.density)
+        self._init_particles(xyzs, covs, volumes)
+
+        # grid, model.py:117-122 -- zero-copy views of the float4 node arrays
+        self.grid_mass = _GridField(b.grid_in, 3)
+        self.grid_v_in = _GridField(b.grid_in, slice(0, 3))
+        self.grid_v_out = _GridField(b.grid_out, slice(0, 3))
+
+    def _init_particles(self, xyzs, covs, volumes):
+        """model.py:101-115 on the packed arrays; physical order == original order afterwards."""
+        b = self._backend
+        n, dev = b.n, b.device
+        if n == 0:
+            return
+        b.reset_order()
+        cur = b.cur
+        vol = volumes.to(device=dev, dtype=torch.float32, non_blocking=True).reshape(n)
+        cur["s1"][:n, 3] = vol
+        cur["meta"][:n, 2] = vol.contiguous().view(torch.int32)
+        compute_mass_from_vol_density(n, self.particle_density.t, vol, cur["xm"][:n, 3])
+        cur["xm"][:n, :3] = xyzs.to(device=dev, dtype=torch.float32, non_blocking=True).reshape(n, 3)
+        cur["vv"][:n].zero_()
+        for a in ("c0", "c1", "cs"):
+            cur[a][:n].zero_()
+        cur["s1"][:n, :3] = 0.0
+        cur["f0"][:n] = torch.tensor([1.0, 0.0, 0.0, 0.0], device=dev)
+        cur["f1"][:n] = torch.tensor([1.0, 0.0, 0.0, 0.0], device=dev)
+        cur["f2"][:n, 0] = 1.0
+        c6 = covs.to(device=dev, dtype=torch.float32, non_blocking=True).reshape(n, 6)
+        if b.ids_init is not None:
+            b.init_cov[b.ids_init[:n].long()] = c6
+        else:
+            b.init_cov.copy_(c6)
+        cur["cv0"][:n] = c6[:, :4]
+        cur["cv1"][:n, :2] = c6[:, 4:]
+        b._ftrial_valid = False
+        b.pristine = True
+        b.stress_dirty = None
+        b.invalidate()
+        b.recompute_keys()
+
+    def reset_grid_state(self):
+        """model.py:124-127.  The substep clears only the blocks it touched; this is the dense version."""
+        self._backend.grid_in.zero_()
+        self._backend.grid_out.zero_()
+
+    def init_identity_mat(self, F):  # model.py:129-132
+        F.fill([1.0, 0.0, 0.0, 0.0, 1.0, 0.0, 0.0, 0.0, 1.0])
+
+
 class MPM_state_opt:
     """model.py:136-223: 31-step history for DiffTaichi system identification -- out of scope."""
 

@@ -19,6 +19,7 @@ from .utils import *            # noqa: F401,F403
 from .utils import _stream, material_types
 from .collider import *         # noqa: F401,F403
 from .boundary_conditions import *  # noqa: F401,F403
+from .fitting import FittingMixin, FittingModel, MPM_state_opt, _FittingBackend   # noqa: F401  (MPM_state_opt: reference name, model.py:136)
 
 
 class _TiShim:
@@ -41,13 +42,25 @@ class _TiShim:
 ti = _TiShim()
 
 
-class MPM_Simulator:
+class MPM_Simulator(FittingMixin):
     def __init__(self, xyzs, covs, volumes, args, init_v=None, strict_q1=True, strict_q3=True, track_cov=False,
-                 capacity=None, ids=None, n_global=None):
-        if getattr(args, "fitting", False):
-            raise NotImplementedError("differentiable path (MPM_state_opt) out of scope")
+                 capacity=None, ids=None, n_global=None, strict_grad=True):
         self.n_particles = xyzs.shape[0]
         device = xyzs.device if xyzs.is_cuda else torch.device("cuda", torch.cuda.current_device())
+        self.fitting = bool(getattr(args, "fitting", False))
+        if self.fitting:
+            # solver.py:14-15: the differentiable state (31-entry history, adjoint fields) and kernels (fitting.py, csrc/opt.cu);
+            # the library context only provides the grid geometry and the stream plumbing here
+            self.strict_grad = bool(strict_grad)
+            self._backend = _FittingBackend(args.n_grid, args.grid_extent, device)
+            self.mpm_model = FittingModel(self.n_particles, args, device, self._backend.ctx)
+            self.mpm_state = MPM_state_opt(self.n_particles, xyzs, covs, volumes, args, init_v, device=device)
+            self.time = 0.0
+            self.collider_params = []
+            self.particle_preprocess = []
+            self.grid_postprocess = []
+            self.init_particles = []
+            return
         self._backend = _Backend(self.n_particles, args.n_grid, args.grid_extent, device, capacity=capacity, ids=ids,
                                  n_global=n_global)
         self.mpm_model = MPM_model(self.n_particles, args, _backend=self._backend)
@@ -167,7 +180,9 @@ class MPM_Simulator:
         ops.n_ops = no
         return ops
 
-    def p2g2p(self, dt):
+    def p2g2p(self, dt, s=None):
+        if self.fitting:   # extra.py:200 calls p2g2p(dt, s) on the fitting simulator
+            return self.p2g2p_forward(dt, 0 if s is None else s)
         b = self._backend
         ops = self._ops_at(self.time)
         b.flush_stress(dt)
@@ -283,9 +298,4 @@ class MPM_Simulator:
         self._backend.ctx.call("mpmk_read_counters", C.byref(c), _stream())
         return {k: getattr(c, k) for k, _ in c._fields_}
 
-    # -- differentiable API of the reference (solver.py:54-108,131-133,168-177): out of scope --
-    def _no_grad(self, *a, **k):
-        raise NotImplementedError("differentiable path out of scope")
-
-    p2g2p_forward = p2g2p_backward = learn = set_bc_ground_only = _no_grad
-    postprocess_forward = postprocess_backward = clear_grads = _no_grad
+    # differentiable API of the reference (solver.py:54-108,131-133,168-177): FittingMixin (fitting.py), needs args.fitting

@@ -279,6 +279,44 @@ MPMK_API int mpmk_mg_halo_exchange(mpmk_ctx* ctx, void* stream);
  * lagged substeps only -- its inverse, the slot g2p moved each particle to.  Any pointer may be NULL.  For tests. */
 MPMK_API int mpmk_get_last_sort(mpmk_ctx* ctx, void* sorted_keys_dev, void* perm_dev, void* rank_dev, void* stream);
 
+/* ---- differentiable ("fitting") path: solver.py:54-108, extra.py:199-236 ---------------------------
+ * Forward kernels with a substep history and hand-written adjoints (csrc/opt.cu) in place of Taichi's autodiff.
+ * All arrays are plain row-major device arrays in ORIGINAL particle order, one substep slice per call:
+ * x, v float[n][3]; F, C, stress float[n][9]; cov, init_cov float[n][6]; mu, lam, logE, y, mass, vol float[n];
+ * grid_v_in, grid_v_out float[n_grid^3][3]; grid_mass float[n_grid^3] (dense, zeroed by the caller per substep as
+ * MPM_state_opt.reset_grid_state does).  g_* are the adjoints (".grad" fields); the *_grad entry points ACCUMULATE
+ * into their outputs like Taichi's reverse-mode kernels.  n_grid, dx, inv_dx come from the context.              */
+/* utils.py:56-76 compute_stress_from_F_opt and its adjoint */
+MPMK_API int mpmk_opt_stress(mpmk_ctx* ctx, int64_t n, const float* F, const float* mu, const float* lam, float* stress, void* stream);
+MPMK_API int mpmk_opt_stress_grad(mpmk_ctx* ctx, int64_t n, const float* F, const float* mu, const float* lam, const float* g_stress,
+                                  float* g_F, float* g_mu, float* g_lam, void* stream);
+/* utils.py:137-174 p2g_opt and its adjoint (grid_mass, mass and vol carry no gradient) */
+MPMK_API int mpmk_opt_p2g(mpmk_ctx* ctx, int64_t n, const float* x, const float* v, const float* C, const float* stress, const float* mass,
+                          const float* vol, float* grid_v_in, float* grid_mass, float dt, void* stream);
+MPMK_API int mpmk_opt_p2g_grad(mpmk_ctx* ctx, int64_t n, const float* x, const float* v, const float* C, const float* stress,
+                               const float* mass, const float* vol, const float* g_grid_v_in, float* g_x, float* g_v, float* g_C,
+                               float* g_stress, float dt, void* stream);
+/* utils.py:178-183 + grid_postprocess[0].apply (boundary_conditions.py:23-27; box_* NULL = none) and their adjoint */
+MPMK_API int mpmk_opt_grid(mpmk_ctx* ctx, const float* grid_v_in, const float* grid_mass, float* grid_v_out, float dt, const float* gravity3,
+                           const float* box_center3, const float* box_size3, void* stream);
+/* block_*: NULL = reference-literal (Taichi leaves the adjoint of a node the box overwrote in place, so its gradient
+ * still flows back); the box = textbook adjoint (nothing flows through a zeroed node) */
+MPMK_API int mpmk_opt_grid_grad(mpmk_ctx* ctx, const float* grid_mass, const float* g_grid_v_out, float* g_grid_v_in,
+                                const float* block_center3, const float* block_size3, void* stream);
+/* utils.py:285-347 g2p_opt (writes slice s+1 from slice s) and its adjoint */
+MPMK_API int mpmk_opt_g2p(mpmk_ctx* ctx, int64_t n, const float* x, const float* F, const float* grid_v_out, float* x1, float* v1, float* C1,
+                          float* F1, float dt, void* stream);
+MPMK_API int mpmk_opt_g2p_grad(mpmk_ctx* ctx, int64_t n, const float* x, const float* F, const float* grid_v_out, const float* g_x1,
+                               const float* g_v1, const float* g_C1, const float* g_F1, float* g_grid_v_out, float* g_x, float* g_F, float dt,
+                               void* stream);
+/* utils.py:436-467 compute_cov_from_F_opt and its adjoint */
+MPMK_API int mpmk_opt_cov(mpmk_ctx* ctx, int64_t n, const float* F, const float* init_cov, float* cov, void* stream);
+MPMK_API int mpmk_opt_cov_grad(mpmk_ctx* ctx, int64_t n, const float* F, const float* init_cov, const float* g_cov, float* g_F, void* stream);
+/* adjoint of utils.py:350-362 compute_mu_lam_from_E_nu, and solver.py:92-108 learn (clipped gradient step) */
+MPMK_API int mpmk_opt_mu_lam_grad(mpmk_ctx* ctx, int64_t n, const float* logE, const float* y, const float* g_mu, const float* g_lam,
+                                  float* g_logE, float* g_y, void* stream);
+MPMK_API int mpmk_opt_learn(mpmk_ctx* ctx, int64_t n, float* logE, float* y, const float* g_logE, const float* g_y, void* stream);
+
 /* ---- introspection -------------------------------------------------------- */
 /* With MPMK_TRACE=1 in the environment: %globaltimer (ns) at the stage boundaries of the last lagged substep of the last
  * batch -- [0] start, [1] p2g done, [2] grid done, [3] g2p done; side branch [5] clear done, [6] sort done, [7] work
