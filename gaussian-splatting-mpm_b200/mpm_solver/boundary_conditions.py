@@ -113,7 +113,7 @@ class MaterialTypeModifier(BasicBC):
 
 class StickyGroundBC(BasicBC):
     """boundary_conditions.py:88-94 skips BasicBC.__init__ (no `type`, no `isCollide`): only usable from
-    the differentiable path, which is out of scope."""
+    the differentiable path (set_bc_ground_only, mpm_solver/fitting.py), which applies it as grid_postprocess[0]."""
 
     def __init__(self):
         self.center = [1.0, 0.6, 1.0]

@@ -485,7 +485,7 @@ class MPM_model:
         b.push_params()
 
     def clear_grad(self):
-        raise NotImplementedError("differentiable path out of scope")
+        raise NotImplementedError("adjoint fields exist on the fitting model only (args.fitting = True: mpm_solver/fitting.py FittingModel)")
 
 
 class MPM_state:
@@ -653,10 +653,3 @@ class MPM_state:
 
     def init_identity_mat(self, F):  # model.py:129-132
         F.fill([1.0, 0.0, 0.0, 0.0, 1.0, 0.0, 0.0, 0.0, 1.0])
-
-
-class MPM_state_opt:
-    """model.py:136-223: 31-step history for DiffTaichi system identification -- out of scope."""
-
-    def __init__(self, *a, **k):
-        raise NotImplementedError("differentiable path out of scope")
