@@ -262,12 +262,13 @@ def run_multi(a, rank, world, local, dev):
                 t.copy_(pin[k], non_blocking=True)
             uploaded[slot].record(ul)
 
-    def e2e_frames(count):
+    def e2e_frames(count, do_up=True, do_down=True):
         ul.wait_stream(stream)                  # no upload of this run starts before the caller's stream reaches it
-        upload(0)
+        if do_up:
+            upload(0)
         for i in range(count):
             slot = i & 1
-            if i + 1 < count:
+            if i + 1 < count and do_up:
                 upload(slot ^ 1)
             st = stage[slot]
             stream.wait_event(uploaded[slot])
@@ -277,11 +278,12 @@ def run_multi(a, rank, world, local, dev):
             stream.wait_event(drained)          # the previous frame's download is done with the export buffers
             b.export(want_R=True)
             ready.record(stream)
-            with torch.cuda.stream(dl):
-                dl.wait_event(ready)
-                out_xyz.copy_(b.out_xyz[rank * n0:(rank + 1) * n0], non_blocking=True)
-                out_cov.copy_(b.out_cov[rank * n0:(rank + 1) * n0], non_blocking=True)
-                drained.record(dl)
+            if do_down:
+                with torch.cuda.stream(dl):
+                    dl.wait_event(ready)
+                    out_xyz.copy_(b.out_xyz[rank * n0:(rank + 1) * n0], non_blocking=True)
+                    out_cov.copy_(b.out_cov[rank * n0:(rank + 1) * n0], non_blocking=True)
+                    drained.record(dl)
         stream.wait_event(drained)              # the last download ends before the caller's stream moves on
 
     for ev in (drained, consumed[0], consumed[1]):
@@ -303,6 +305,11 @@ def run_multi(a, rank, world, local, dev):
             lap("d2h", lambda: (out_xyz.copy_(b.out_xyz[rank * n0:(rank + 1) * n0], non_blocking=True), out_cov.copy_(b.out_cov[rank * n0:(rank + 1) * n0], non_blocking=True)))
         if rank == 0:
             print("frame phases, ms (3 frames, serialised):", {k: round(v / 3, 2) for k, v in ph.items()}, file=sys.stderr, flush=True)
+        abl = {}
+        for name, (u_, d_) in (("no copies", (False, False)), ("uploads only", (True, False)), ("downloads only", (False, True)), ("both", (True, True))):
+            abl[name] = round(timed(lambda: e2e_frames(ke, u_, d_), 1) / ke, 2)
+        if rank == 0:
+            print("frame loop ablation, ms per frame:", abl, file=sys.stderr, flush=True)
     peak, peak_src = _peaks()
     sub_bytes = 216.0 * N + 72.0 * float(touched.item())
     allin_ms = ms / (a.steps * S)

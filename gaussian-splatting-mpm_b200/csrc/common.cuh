@@ -278,8 +278,10 @@ struct BatchDesc {
 };
 
 // Warp-uniform stream of batches over dynamically fetched work items (one atomic on the cursor per item).
-// Requesting the next item ahead of time was tried and measured slower: a warp that reserves an item
-// early lengthens the tail of the persistent grid (items are coarse, ~3.5 per warp at 4 M particles).
+// Requesting the next item ahead of time was tried twice and is not worth it: a whole item ahead is slower (a warp that
+// reserves an item early lengthens the tail of the persistent grid; items are coarse, ~7 per warp at 4 M particles), and
+// taking the ticket one batch ahead (the atomic's round trip, 8 % of g2p's stall samples, then overlaps a batch of work)
+// measures the same as waiting for it: other warps fill the gap.
 struct BatchStream {
     uint4 item;  // current item {begin, count, tile, -}
     uint32_t off;

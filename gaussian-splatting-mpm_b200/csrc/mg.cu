@@ -185,6 +185,9 @@ __global__ void k_halo_add(float4* __restrict__ gin, const float4* __restrict__ 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
     uint32_t v;
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -232,13 +235,21 @@ __global__ void __launch_bounds__(256) k_halo_push(const float4* __restrict__ gi
         const float4 v = gin[(((int64_t)((up ? hi.x0 : lo.x0) + px) * n + y0 + py) * n) + z0 + pz];
         (up ? peer_hi : peer_lo)[par + j] = v;
     }
-    __threadfence_system();
+    // One system-scope fence per push, not one per thread.  The block's stores reach thread 0 through the barrier, its
+    // device-scope fence orders them before the block counter, and the last block out -- which has observed every other
+    // block's counter update -- issues the one fence.acq_rel.sys that, being cumulative, orders ALL of the push's stores
+    // before the two flag stores.  (__threadfence_system() is fence.sc.sys: MEMBAR.SC.SYS + ERRBAR + CCTL.IVALL in every
+    // warp, and a system-scope fence queues behind whatever the copy engines have in flight towards the host: with a
+    // frame's download running beside the substeps, 75 k of them per push cost the 8-GPU frame loop 11 ms per frame.)
     __syncthreads();
-    if (threadIdx.x == 0 && atomicAdd(&my_ctrl[MGP_DONE_LO], 1u) == gridDim.x - 1) {
-        my_ctrl[MGP_DONE_LO] = 0u;
-        __threadfence_system();
-        if (lo.nx > 0) st_release_sys(flag_lo, e + 1u);
-        if (hi.nx > 0) st_release_sys(flag_hi, e + 1u);
+    if (threadIdx.x == 0) {
+        asm volatile("fence.acq_rel.gpu;" ::: "memory");
+        if (atomicAdd(&my_ctrl[MGP_DONE_LO], 1u) == gridDim.x - 1) {
+            my_ctrl[MGP_DONE_LO] = 0u;
+            asm volatile("fence.acq_rel.sys;" ::: "memory");
+            if (lo.nx > 0) st_relaxed_sys(flag_lo, e + 1u);
+            if (hi.nx > 0) st_relaxed_sys(flag_hi, e + 1u);
+        }
     }
 }
 
@@ -592,3 +603,21 @@ extern "C" int mpmk_mg_close_holes(mpmk_ctx* ctx, const void* holes_dev, int64_t
     MPMK_LAUNCH_CHECK(ctx);
     return 0;
 }
+
+// ---- small read-back past the copy engines (mpmk.h: mpmk_read_small) ----------------------------------------
+__global__ void k_store_host(uint32_t* __restrict__ dst, const uint32_t* __restrict__ src, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[i];
+    __threadfence_system();
+}
+
+extern "C" int mpmk_read_small(mpmk_ctx* ctx, void* dst_pinned, const void* src_dev, int n_words, void* stream) {
+    if (!ctx || !dst_pinned || !src_dev || n_words < 0) return MPMK_ERR_INVALID;
+    if (n_words == 0) return 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    k_store_host<<<div_up(n_words, 256), 256, 0, s>>>((uint32_t*)dst_pinned, (const uint32_t*)src_dev, n_words);
+    MPMK_LAUNCH_CHECK(ctx);
+    MPMK_CHECK(ctx, cudaStreamSynchronize(s));
+    return 0;
+}
+

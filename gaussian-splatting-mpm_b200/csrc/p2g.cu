@@ -86,6 +86,15 @@ __device__ __forceinline__ void p2g_flush_run(const P2GArgs& a, float4* tile, in
     }
 }
 
+// The velocity record is read as 8 + 4 bytes: its fourth component is padding, and ptxas hands the register of a dead
+// component of a prefetched 16-byte load to a temporary of phase B, whose first write then has to wait for the whole
+// prefetch to land (a write-after-write hazard on the loads' scoreboard: 8 % of the kernel's stall samples sat there).
+__device__ __forceinline__ float4 p2g_ldg_vel(const float4* p) {
+    const float2 xy = __ldg(reinterpret_cast<const float2*>(p));
+    const float z = __ldg(reinterpret_cast<const float*>(p) + 2);
+    return make_float4(xy.x, xy.y, z, 0.f);
+}
+
 template <bool LAG>
 __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GArgs a) {
     pdl_wait();   // programmatic dependent launch: nothing of the previous grid is read or overwritten before this
@@ -121,7 +130,7 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
     float4 Xn = zero4, Vn = zero4, C0n = zero4, C1n = zero4, CSn = zero4, S1n = zero4;
     if (lane < dA.count) {
-        Xn = __ldg(a.xm + pA); Vn = __ldg(a.vv + pA); C0n = __ldg(a.c0 + pA);
+        Xn = __ldg(a.xm + pA); Vn = p2g_ldg_vel(a.vv + pA); C0n = __ldg(a.c0 + pA);
         C1n = __ldg(a.c1 + pA); CSn = __ldg(a.cs + pA); S1n = __ldg(a.s1 + pA);
     }
     int cur_cell = -1;
@@ -221,7 +230,7 @@ __global__ void __launch_bounds__(P2G_WARPS * 32, P2G_MIN_CTAS) k_p2g(const P2GA
             }
             // batch B's records: in flight during phase B
             if (lane < dB.count) {
-                Xn = __ldg(a.xm + pB); Vn = __ldg(a.vv + pB); C0n = __ldg(a.c0 + pB);
+                Xn = __ldg(a.xm + pB); Vn = p2g_ldg_vel(a.vv + pB); C0n = __ldg(a.c0 + pB);
                 C1n = __ldg(a.c1 + pB); CSn = __ldg(a.cs + pB); S1n = __ldg(a.s1 + pB);
             }
             __syncwarp();

@@ -145,6 +145,7 @@ def lib():
         "mpmk_mg_peer_enabled": (i, [vp]),
         "mpmk_mg_peer_close": (i, [vp]),
         "mpmk_mg_set_count": (i, [vp, i64]),
+        "mpmk_read_small": (i, [vp, vp, vp, i, vp]),
         "mpmk_mg_scan": (i, [vp, vp, vp, vp, vp]),
         "mpmk_mg_pack": (i, [vp, vp, i64, vp, vp]),
         "mpmk_mg_unpack": (i, [vp, vp, i64, i64, vp, vp]),

@@ -439,8 +439,8 @@ class MPM_model:
             mu = torch.empty(1, dtype=torch.float32, device=b.device)
             lam = torch.empty(1, dtype=torch.float32, device=b.device)
             compute_mu_lam_from_E_nu(b.ctx, 1, self._logE[:1].contiguous(), self._y[:1].contiguous(), mu, lam)
-            self.mu.fill(float(mu.item()))
-            self.lam.fill(float(lam.item()))
+            self.mu.fill(mu)      # device scalars, broadcast on the device: no host round trip (a reload per frame would
+            self.lam.fill(lam)    # queue two 4-byte downloads behind whatever bulk copy the caller has in flight)
             return
         mu = torch.empty(n, dtype=torch.float32, device=b.device)
         lam = torch.empty(n, dtype=torch.float32, device=b.device)
@@ -546,8 +546,9 @@ class MPM_state:
         for a in ("c0", "c1", "cs"):
             cur[a][:n].zero_()
         cur["s1"][:n, :3] = 0.0
-        cur["f0"][:n] = torch.tensor([1.0, 0.0, 0.0, 0.0], device=dev)
-        cur["f1"][:n] = torch.tensor([1.0, 0.0, 0.0, 0.0], device=dev)
+        for a in ("f0", "f1"):     # F = I: (1, 0, 0, 0), (1, 0, 0, 0), (1, ...)
+            cur[a][:n].zero_()
+            cur[a][:n, 0] = 1.0
         cur["f2"][:n, 0] = 1.0
         c6 = covs.to(device=dev, dtype=torch.float32, non_blocking=True).reshape(n, 6)
         if b.ids_init is not None:
@@ -630,8 +631,9 @@ class MPM_state:
         for a in ("c0", "c1", "cs"):
             cur[a][:n].zero_()
         cur["s1"][:n, :3] = 0.0
-        cur["f0"][:n] = torch.tensor([1.0, 0.0, 0.0, 0.0], device=dev)
-        cur["f1"][:n] = torch.tensor([1.0, 0.0, 0.0, 0.0], device=dev)
+        for a in ("f0", "f1"):     # F = I: (1, 0, 0, 0), (1, 0, 0, 0), (1, ...)
+            cur[a][:n].zero_()
+            cur[a][:n, 0] = 1.0
         cur["f2"][:n, 0] = 1.0
         c6 = covs.to(device=dev, dtype=torch.float32, non_blocking=True).reshape(n, 6)
         if b.ids_init is not None:

@@ -228,6 +228,16 @@ class CudaRecordOps:
         self.b.ctx.call("mpmk_mg_scan", self.stats.data_ptr(), self.idx_lo.data_ptr(), self.idx_hi.data_ptr(), self._stream())
         return self.stats[:SCAN_WIDTH].to(torch.int64)
 
+    def to_host(self, t):
+        """a small device tensor on the host without a copy engine (mpmk_read_small): `.cpu()` would queue behind any bulk
+        download the caller has in flight on another stream -- a frame loop that streams its results out"""
+        t = t.contiguous()
+        words = t.numel() * t.element_size() // 4
+        if getattr(self, "_pin", None) is None or self._pin.numel() < words:
+            self._pin = torch.empty(max(words, 1024), dtype=torch.int32).pin_memory()
+        self.b.ctx.call("mpmk_read_small", self._pin.data_ptr(), t.data_ptr(), words, self._stream())
+        return self._pin[:words].clone().view(t.dtype).reshape(t.shape)
+
     def pack_leavers(self, n_lo, n_hi):
         self.n_lo, self.n_hi = n_lo, n_hi
         out = []
@@ -281,7 +291,8 @@ def migrate(store: dict, n: int, capacity: int, bounds, rank: int, ghost: int, n
     else:
         table[:SCAN_WIDTH] = mine
     _mark("scan", device)
-    table = table.view(world, SCAN_WIDTH).cpu()           # the one synchronisation
+    # the one synchronisation
+    table = ops.to_host(table).view(world, SCAN_WIDTH) if hasattr(ops, "to_host") else table.view(world, SCAN_WIDTH).cpu()
     _mark("allgather+sync", device)
     if int(table[:, 8].max()):     # collective: every rank sees the same table, every rank raises
         bad = [r for r in range(world) if int(table[r, 8])]
@@ -314,7 +325,7 @@ def migrate(store: dict, n: int, capacity: int, bounds, rank: int, ghost: int, n
     return n_new, stats
 
 
-def global_row_range(store: dict, n: int, nt: int, n_grid: int, margin: int, group=None, axis="y"):
+def global_row_range(store: dict, n: int, nt: int, n_grid: int, margin: int, group=None, axis="y", to_host=None):
     """[y_lo, y_hi): rows of the shared planes any rank's stencils can reach before the next migration (axis="z": the
     same along the fastest axis)"""
     device = store["keys"].device
@@ -327,7 +338,8 @@ def global_row_range(store: dict, n: int, nt: int, n_grid: int, margin: int, gro
     v = torch.stack([-lo, hi]).to(torch.int64)
     if dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(v, op=dist.ReduceOp.MAX, group=group)
-    lo, hi = -int(v[0].item()), int(v[1].item())
+    v = to_host(v) if to_host is not None else v.cpu()
+    lo, hi = -int(v[0]), int(v[1])
     if hi < lo:
         return 0, n_grid
     return max(0, lo - margin), min(n_grid, hi + 3 + margin)
@@ -473,8 +485,9 @@ class SlabSimulator:
 
     def _set_slab(self, rows=None, zs=None):
         b = self.backend
-        y_lo, y_hi = rows if rows is not None else global_row_range(self._store(), b.n, self.nt, self.n_grid, self.ghost + 1, self.group)
-        z_lo, z_hi = zs if zs is not None else global_row_range(self._store(), b.n, self.nt, self.n_grid, self.ghost + 1, self.group, axis="z")
+        rd = self._ops.to_host
+        y_lo, y_hi = rows if rows is not None else global_row_range(self._store(), b.n, self.nt, self.n_grid, self.ghost + 1, self.group, to_host=rd)
+        z_lo, z_hi = zs if zs is not None else global_row_range(self._store(), b.n, self.nt, self.n_grid, self.ghost + 1, self.group, axis="z", to_host=rd)
         self.rows, self.zs = (y_lo, y_hi), (z_lo, z_hi)
         b.ctx.call("mpmk_mg_set_slab", self.bounds[self.rank], self.bounds[self.rank + 1], self.ghost, y_lo, y_hi,
                    self._recv_lo.data_ptr() if self._recv_lo is not None else None,

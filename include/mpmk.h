@@ -241,6 +241,13 @@ MPMK_API int mpmk_mg_set_window(mpmk_ctx* ctx, int z_lo, int z_hi);
 /* peer-memory halo: substep epoch at which this rank gave up waiting (4 s) for a neighbour's push; 0 = never.
  * Synchronises `stream`.  mpmk_mg_scan also reports it in stats[8], which is how slabs.py raises on every rank. */
 MPMK_API int mpmk_mg_peer_error(mpmk_ctx* ctx, uint32_t* epoch_out, void* stream);
+/* Small device -> host read-back that does not use a copy engine: a kernel stores `n_words` 32-bit words from
+ * `src_dev` into `dst_pinned`, page-locked host memory the device can address (cudaHostAlloc / torch pin_memory()
+ * under unified addressing), and `stream` is synchronised.  A cudaMemcpy of a few bytes queues on the device-to-host
+ * copy engine behind whatever bulk download the caller has in flight on another stream (measured at 8 GPUs: the 72-byte
+ * migration table waited ~12 ms per frame behind the previous frame's 147 MB download); a store from an SM does not.
+ * No reference counterpart (slab plumbing, mpm_solver/slabs.py).                                              */
+MPMK_API int mpmk_read_small(mpmk_ctx* ctx, void* dst_pinned, const void* src_dev, int n_words, void* stream);
 /* new live particle count after a host-side migration (mpm_solver/slabs.py); unlike mpmk_set_count
  * it keeps the current set and the validity of the stored F_trial records                       */
 MPMK_API int mpmk_mg_set_count(mpmk_ctx* ctx, int64_t n_particles);
