@@ -53,6 +53,7 @@ struct MgState {
     unsigned char* my_block;
     unsigned char* peer_block[2];   // [0] rank-1's block, [1] rank+1's block
     size_t buf_bytes;               // one receive buffer
+    size_t msg_bytes;               // one message slot (mpmk_mg_ll_send / _recv: the migration payload), 0 = none
 };
 
 struct mpmk_ctx {

@@ -285,6 +285,81 @@ __global__ void __launch_bounds__(256) k_halo_wait_add(float4* __restrict__ gin,
     }
 }
 
+// ---- the same exchange without any fence: every 8 bytes carry their own flag ("LL" protocol) ---------------------
+// A node travels as two 16-byte stores {p_x, f, p_y, f} {p_z, f, m, f} with f = epoch + 1 (never 0, never a value an
+// earlier use of the buffer left behind: epochs only grow).  NVLink delivers aligned 8-byte words whole, so a receiver
+// that reads a word with the right flag has its payload: no flag word per push, no block counter, and above all no
+// system-scope fence on either side.  A fence.sys waits for everything the GPU has in flight towards the system, which
+// includes a copy engine's bulk download to the host: with 8 GPUs streaming results out over a shared PCIe root, the one
+// fence per push that the flag protocol needs cost 0.15 ms per substep.  Twice the bytes over NVLink (2 x 1.2 MB per
+// neighbour and substep) is nothing beside that.
+__device__ __forceinline__ void st_volatile_v4(uint4* p, uint4 v) {
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 ld_volatile_v4(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(256) k_halo_push_ll(const float4* __restrict__ gin, uint4* __restrict__ peer_lo, uint4* __restrict__ peer_hi,
+                                                      size_t buf_u4, const uint32_t* my_ctrl, MgRegion lo, MgRegion hi, int y0, int ny,
+                                                      int z0, int nz, int n) {
+    const uint32_t e = my_ctrl[MGP_EPOCH];
+    const uint32_t f = e + 1u;
+    const size_t par = (size_t)(e & 1u) * buf_u4;
+    const int64_t per_plane = (int64_t)ny * nz;
+    const int64_t tlo = per_plane * lo.nx, total = tlo + per_plane * hi.nx;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const bool up = i >= tlo;
+        const int64_t j = up ? i - tlo : i;
+        const int64_t px = j / per_plane, rem = j - px * per_plane;
+        const int64_t py = rem / nz, pz = rem - py * nz;
+        const float4 v = gin[(((int64_t)((up ? hi.x0 : lo.x0) + px) * n + y0 + py) * n) + z0 + pz];
+        uint4* dst = (up ? peer_hi : peer_lo) + par + 2 * j;
+        st_volatile_v4(dst, make_uint4(__float_as_uint(v.x), f, __float_as_uint(v.y), f));
+        st_volatile_v4(dst + 1, make_uint4(__float_as_uint(v.z), f, __float_as_uint(v.w), f));
+    }
+}
+
+// add both neighbours' pushes of this epoch as their words arrive (a + b here, b + a there: bit-identical sums), advance
+// the epoch.  A word that has not arrived after MGP_SPIN_NS sets the error word (see mg_wait_flag) and counts as zero.
+__global__ void __launch_bounds__(256) k_halo_wait_add_ll(float4* __restrict__ gin, const uint4* __restrict__ buf_lo,
+                                                          const uint4* __restrict__ buf_hi, size_t buf_u4, uint32_t* my_ctrl, MgRegion lo,
+                                                          MgRegion hi, int y0, int ny, int z0, int nz, int n) {
+    const uint32_t e = my_ctrl[MGP_EPOCH];
+    const uint32_t f = e + 1u;
+    const int64_t per_plane = (int64_t)ny * nz;
+    const int64_t tlo = per_plane * lo.nx, total = tlo + per_plane * hi.nx;
+    const uint4* blo = buf_lo + (size_t)(e & 1u) * buf_u4;
+    const uint4* bhi = buf_hi + (size_t)(e & 1u) * buf_u4;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const bool up = i >= tlo;
+        const int64_t j = up ? i - tlo : i;
+        const int64_t px = j / per_plane, rem = j - px * per_plane;
+        const int64_t py = rem / nz, pz = rem - py * nz;
+        float4* g = gin + ((((int64_t)((up ? hi.x0 : lo.x0) + px) * n + y0 + py) * n) + z0 + pz);
+        const uint4* src = (up ? bhi : blo) + 2 * j;
+        uint4 w0 = ld_volatile_v4(src), w1 = ld_volatile_v4(src + 1);
+        if (w0.y != f || w0.w != f || w1.y != f || w1.w != f) {
+            const unsigned long long t0 = mg_now_ns();
+            for (;;) {
+                w0 = ld_volatile_v4(src); w1 = ld_volatile_v4(src + 1);
+                if (w0.y == f && w0.w == f && w1.y == f && w1.w == f) break;
+                if (mg_now_ns() - t0 > MGP_SPIN_NS) { my_ctrl[MGP_ERR] = f; w0.x = w0.z = w1.x = w1.z = 0u; break; }
+            }
+        }
+        float4 a = *g;
+        a.x += __uint_as_float(w0.x); a.y += __uint_as_float(w0.z); a.z += __uint_as_float(w1.x); a.w += __uint_as_float(w1.z);
+        *g = a;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && atomicAdd(&my_ctrl[MGP_DONE_ADD], 1u) == gridDim.x - 1) {
+        my_ctrl[MGP_DONE_ADD] = 0u;
+        my_ctrl[MGP_EPOCH] = e + 1u;   // read by the next substep's kernels (later launches on the stream)
+    }
+}
+
 static int halo_sum_peer(mpmk_ctx* ctx, cudaStream_t s) {
     const MgState& m = ctx->mg;
     const int n = ctx->n_grid, ny = m.y_hi - m.y_lo, nz = m.z_hi - m.z_lo;
@@ -293,16 +368,32 @@ static int halo_sum_peer(mpmk_ctx* ctx, cudaStream_t s) {
     uint32_t* my_ctrl = (uint32_t*)m.my_block;
     float4* gin = (float4*)ctx->b.grid_in;
     const MgRegion lo = {m.lo0, m.lo1 - m.lo0}, hi = {m.hi0, m.hi1 - m.hi0};
+    // every buffer is a slot of 2 x buf_bytes: the dense float4 image under the flag protocol, 32-byte flagged nodes under LL;
+    // side s, parity p at slot 2 s + p
+    const size_t slot = 2 * m.buf_bytes;
+    static const bool ll = !(getenv("MPMK_MG_LL") && atoi(getenv("MPMK_MG_LL")) == 0);
+    if (ll) {
+        // my data for rank-1 lands in ITS side-1 slots (I am its rank+1); for rank+1: side 0
+        uint4* pl = lo.nx > 0 ? (uint4*)(m.peer_block[0] + MGP_CTRL_BYTES + 2 * slot) : nullptr;
+        uint4* ph = hi.nx > 0 ? (uint4*)(m.peer_block[1] + MGP_CTRL_BYTES) : nullptr;
+        k_halo_push_ll<<<ctx->sm_count * 2, 256, 0, s>>>(gin, pl, ph, slot / 16, my_ctrl, lo, hi, m.y_lo, ny, m.z_lo, nz, n);
+        MPMK_LAUNCH_CHECK(ctx);
+        const uint4* ml = (const uint4*)(m.my_block + MGP_CTRL_BYTES);
+        const uint4* mh = (const uint4*)(m.my_block + MGP_CTRL_BYTES + 2 * slot);
+        k_halo_wait_add_ll<<<ctx->sm_count * 2, 256, 0, s>>>(gin, ml, mh, slot / 16, my_ctrl, lo, hi, m.y_lo, ny, m.z_lo, nz, n);
+        MPMK_LAUNCH_CHECK(ctx);
+        return 0;
+    }
     // my data for rank-1 lands in ITS side-1 buffers (I am its rank+1) and raises its FLAG_HI; for rank+1: side 0, FLAG_LO
-    float4* pb_lo = lo.nx > 0 ? (float4*)(m.peer_block[0] + MGP_CTRL_BYTES + 2 * m.buf_bytes) : nullptr;
+    float4* pb_lo = lo.nx > 0 ? (float4*)(m.peer_block[0] + MGP_CTRL_BYTES + 2 * slot) : nullptr;
     float4* pb_hi = hi.nx > 0 ? (float4*)(m.peer_block[1] + MGP_CTRL_BYTES) : nullptr;
     uint32_t* fl_lo = lo.nx > 0 ? (uint32_t*)m.peer_block[0] + MGP_FLAG_HI : nullptr;
     uint32_t* fl_hi = hi.nx > 0 ? (uint32_t*)m.peer_block[1] + MGP_FLAG_LO : nullptr;
-    k_halo_push<<<ctx->sm_count * 2, 256, 0, s>>>(gin, pb_lo, pb_hi, buf_f4, fl_lo, fl_hi, my_ctrl, lo, hi, m.y_lo, ny, m.z_lo, nz, n);
+    k_halo_push<<<ctx->sm_count * 2, 256, 0, s>>>(gin, pb_lo, pb_hi, slot / 16, fl_lo, fl_hi, my_ctrl, lo, hi, m.y_lo, ny, m.z_lo, nz, n);
     MPMK_LAUNCH_CHECK(ctx);
     const float4* my_lo = (const float4*)(m.my_block + MGP_CTRL_BYTES);
-    const float4* my_hi = (const float4*)(m.my_block + MGP_CTRL_BYTES + 2 * m.buf_bytes);
-    k_halo_wait_add<<<ctx->sm_count * 2, 256, 0, s>>>(gin, my_lo, my_hi, buf_f4, my_ctrl, lo, hi, m.y_lo, ny, m.z_lo, nz, n);
+    const float4* my_hi = (const float4*)(m.my_block + MGP_CTRL_BYTES + 2 * slot);
+    k_halo_wait_add<<<ctx->sm_count * 2, 256, 0, s>>>(gin, my_lo, my_hi, slot / 16, my_ctrl, lo, hi, m.y_lo, ny, m.z_lo, nz, n);
     MPMK_LAUNCH_CHECK(ctx);
     return 0;
 }
@@ -317,13 +408,18 @@ extern "C" int mpmk_mg_peer_error(mpmk_ctx* ctx, uint32_t* epoch_out, void* stre
     return 0;
 }
 
-// allocate this rank's exchange block and export it; handle_out receives the 64-byte cudaIpcMemHandle_t
-extern "C" int mpmk_mg_peer_alloc(mpmk_ctx* ctx, int64_t buf_bytes, void* handle_out, int handle_bytes) {
-    if (!ctx || !handle_out || handle_bytes < (int)sizeof(cudaIpcMemHandle_t) || buf_bytes <= 0 || (buf_bytes & 15)) return MPMK_ERR_INVALID;
+// allocate this rank's exchange block and export it; handle_out receives the 64-byte cudaIpcMemHandle_t.
+// Layout: control words, 2 sides x 2 parities of halo slots (a slot = 2 x buf_bytes, halo_sum_peer), then 2 sides x 2
+// parities of message slots of msg_bytes (mpmk_mg_ll_send / _recv).
+extern "C" int mpmk_mg_peer_alloc_ex(mpmk_ctx* ctx, int64_t buf_bytes, int64_t msg_bytes, void* handle_out, int handle_bytes) {
+    if (!ctx || !handle_out || handle_bytes < (int)sizeof(cudaIpcMemHandle_t) || buf_bytes <= 0 || (buf_bytes & 15) || msg_bytes < 0 ||
+        (msg_bytes & 15))
+        return MPMK_ERR_INVALID;
     MgState& m = ctx->mg;
     if (m.my_block) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_mg_peer_alloc: already allocated");
     MPMK_CHECK(ctx, cudaSetDevice(ctx->device));
-    const size_t total = MGP_CTRL_BYTES + 4 * (size_t)buf_bytes;
+    const size_t total = MGP_CTRL_BYTES + 4 * 2 * (size_t)buf_bytes + 4 * (size_t)msg_bytes;
+    m.msg_bytes = (size_t)msg_bytes;
     MPMK_CHECK(ctx, cudaMalloc((void**)&m.my_block, total));
     MPMK_CHECK(ctx, cudaMemset(m.my_block, 0, total));
     MPMK_CHECK(ctx, cudaDeviceSynchronize());
@@ -331,6 +427,78 @@ extern "C" int mpmk_mg_peer_alloc(mpmk_ctx* ctx, int64_t buf_bytes, void* handle
     MPMK_CHECK(ctx, cudaIpcGetMemHandle(&h, m.my_block));
     memcpy(handle_out, &h, sizeof(h));
     m.buf_bytes = (size_t)buf_bytes;
+    return 0;
+}
+
+extern "C" int mpmk_mg_peer_alloc(mpmk_ctx* ctx, int64_t buf_bytes, void* handle_out, int handle_bytes) {
+    return mpmk_mg_peer_alloc_ex(ctx, buf_bytes, 0, handle_out, handle_bytes);
+}
+
+// ---- flagged messages between neighbours (the migration payload) ---------------------------------------------------
+// The LL encoding of the halo on an arbitrary word array: words (2 i, 2 i + 1) travel as one 16-byte store
+// {w0, tag, w1, tag} into the neighbour's message slot [side][tag & 1]; the receiver spins per 16 bytes until both tags
+// match.  No NCCL, no fence, no rendezvous: under a congested host link (8 GPUs downloading a frame each) ncclSend /
+// ncclRecv of the migration records took ~6 ms per migration -- their chunk hand-shakes are system-scope fences -- against
+// 0.15 ms for the same records without contention.  `tag` must differ from the tag of the previous message through the
+// same slot and must not be 0; both sides pass the same value (the migration count).
+__global__ void __launch_bounds__(256) k_ll_send(uint4* __restrict__ dst, const uint32_t* __restrict__ src, int64_t n_words, uint32_t tag) {
+    const int64_t pairs = (n_words + 1) / 2;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < pairs; i += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t w0 = src[2 * i], w1 = (2 * i + 1 < n_words) ? src[2 * i + 1] : 0u;
+        st_volatile_v4(dst + i, make_uint4(w0, tag, w1, tag));
+    }
+}
+
+__global__ void __launch_bounds__(256) k_ll_recv(uint32_t* __restrict__ dst, const uint4* __restrict__ src, int64_t n_words, uint32_t tag,
+                                                 uint32_t* err) {
+    const int64_t pairs = (n_words + 1) / 2;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < pairs; i += (int64_t)gridDim.x * blockDim.x) {
+        uint4 w = ld_volatile_v4(src + i);
+        if (w.y != tag || w.w != tag) {
+            const unsigned long long t0 = mg_now_ns();
+            for (;;) {
+                w = ld_volatile_v4(src + i);
+                if (w.y == tag && w.w == tag) break;
+                if (mg_now_ns() - t0 > MGP_SPIN_NS) { *err = 0x80000000u | tag; w.x = w.z = 0u; break; }
+            }
+        }
+        dst[2 * i] = w.x;
+        if (2 * i + 1 < n_words) dst[2 * i + 1] = w.z;
+    }
+}
+
+static unsigned char* mg_msg_slot(const MgState& m, unsigned char* block, int side, uint32_t tag) {
+    return block + MGP_CTRL_BYTES + 4 * 2 * m.buf_bytes + (size_t)(2 * side + (int)(tag & 1u)) * m.msg_bytes;
+}
+
+// side 0: to rank-1 (lands in ITS side-1 slots), side 1: to rank+1 (its side-0 slots)
+extern "C" int mpmk_mg_ll_send(mpmk_ctx* ctx, int side, const void* src_dev, int64_t n_words, uint32_t tag, void* stream) {
+    if (!ctx || side < 0 || side > 1 || n_words < 0 || tag == 0u) return MPMK_ERR_INVALID;
+    const MgState& m = ctx->mg;
+    if (!m.peer || !m.peer_block[side]) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_mg_ll_send: no mapped neighbour on that side");
+    if ((size_t)((n_words + 1) / 2) * 16 > m.msg_bytes) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_mg_ll_send: message larger than the slot");
+    if (n_words == 0) return 0;
+    if (!src_dev) return MPMK_ERR_INVALID;
+    const int64_t pairs = (n_words + 1) / 2;
+    const int grid = (int)(pairs / 256 + 1 < (int64_t)ctx->sm_count * 4 ? pairs / 256 + 1 : (int64_t)ctx->sm_count * 4);
+    k_ll_send<<<grid, 256, 0, (cudaStream_t)stream>>>((uint4*)mg_msg_slot(m, m.peer_block[side], 1 - side, tag), (const uint32_t*)src_dev, n_words, tag);
+    MPMK_LAUNCH_CHECK(ctx);
+    return 0;
+}
+
+// side 0: from rank-1, side 1: from rank+1
+extern "C" int mpmk_mg_ll_recv(mpmk_ctx* ctx, int side, void* dst_dev, int64_t n_words, uint32_t tag, void* stream) {
+    if (!ctx || side < 0 || side > 1 || n_words < 0 || tag == 0u) return MPMK_ERR_INVALID;
+    const MgState& m = ctx->mg;
+    if (!m.peer || !m.my_block) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_mg_ll_recv: peer-memory path is not open");
+    if ((size_t)((n_words + 1) / 2) * 16 > m.msg_bytes) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_mg_ll_recv: message larger than the slot");
+    if (n_words == 0) return 0;
+    if (!dst_dev) return MPMK_ERR_INVALID;
+    const int64_t pairs = (n_words + 1) / 2;
+    const int grid = (int)(pairs / 256 + 1 < (int64_t)ctx->sm_count * 4 ? pairs / 256 + 1 : (int64_t)ctx->sm_count * 4);
+    k_ll_recv<<<grid, 256, 0, (cudaStream_t)stream>>>((uint32_t*)dst_dev, (const uint4*)mg_msg_slot(m, m.my_block, side, tag), n_words, tag,
+                                                      (uint32_t*)m.my_block + MGP_ERR);
+    MPMK_LAUNCH_CHECK(ctx);
     return 0;
 }
 

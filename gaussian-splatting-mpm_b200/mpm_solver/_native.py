@@ -141,6 +141,9 @@ def lib():
         "mpmk_mg_peer_error": (i, [vp, C.POINTER(C.c_uint32), vp]),
         "mpmk_mg_halo_exchange": (i, [vp, vp]),
         "mpmk_mg_peer_alloc": (i, [vp, i64, vp, i]),
+        "mpmk_mg_peer_alloc_ex": (i, [vp, i64, i64, vp, i]),
+        "mpmk_mg_ll_send": (i, [vp, i, vp, i64, C.c_uint32, vp]),
+        "mpmk_mg_ll_recv": (i, [vp, i, vp, i64, C.c_uint32, vp]),
         "mpmk_mg_peer_open": (i, [vp, vp, vp]),
         "mpmk_mg_peer_enabled": (i, [vp]),
         "mpmk_mg_peer_close": (i, [vp]),

@@ -247,6 +247,25 @@ class CudaRecordOps:
             out.append(rows)
         return out
 
+    msg_records = 0   # > 0: neighbours' exchange blocks are mapped with message slots for that many records
+    _tag = 0
+
+    def exchange(self, send_lo, send_hi, n_from_lo, n_from_hi):
+        """the payload as flagged 16-byte stores straight into the neighbours' message slots (mpmk_mg_ll_send / _recv):
+        both sends, then both receives, all on the simulator's stream; every rank takes this path for a given migration
+        or none does (the caller decides from the all-gathered table); the tag is the migration count"""
+        call, st = self.b.ctx.call, self._stream()
+        recv_lo = torch.empty((n_from_lo, RECORD_WIDTH), dtype=torch.int32, device=self.device)
+        recv_hi = torch.empty((n_from_hi, RECORD_WIDTH), dtype=torch.int32, device=self.device)
+        for side, snd in ((0, send_lo), (1, send_hi)):
+            if snd.shape[0]:
+                snd = snd.contiguous()
+                call("mpmk_mg_ll_send", side, snd.data_ptr(), snd.numel(), self._tag, st)
+        for side, rcv in ((0, recv_lo), (1, recv_hi)):
+            if rcv.shape[0]:
+                call("mpmk_mg_ll_recv", side, rcv.data_ptr(), rcv.numel(), self._tag, st)
+        return recv_lo, recv_hi
+
     def refill(self, n, n_new, arrivals):
         call, st = self.b.ctx.call, self._stream()
         L, R = self.n_lo + self.n_hi, int(arrivals.shape[0])
@@ -284,6 +303,8 @@ def migrate(store: dict, n: int, capacity: int, bounds, rank: int, ghost: int, n
     if ops is None:
         ops = TorchRecordOps(store, nt, n_grid)
     _mark("begin", device)
+    if hasattr(ops, "exchange"):
+        ops._tag += 1          # the message tag = the migration count: in step on every rank, whoever has something to send
     mine = ops.scan(n, x_lo, x_hi, ghost)
     table = torch.empty(world * SCAN_WIDTH, dtype=torch.int64, device=device)
     if world > 1:
@@ -318,7 +339,10 @@ def migrate(store: dict, n: int, capacity: int, bounds, rank: int, ghost: int, n
         raise SlabError(f"rank {rank}: {n_new} particles after migration exceed the capacity {capacity}")
     send_lo, send_hi = ops.pack_leavers(n_lo, n_hi)
     _mark("pack", device)
-    recv_lo, recv_hi = _payload_exchange(send_lo, send_hi, n_from_lo, n_from_hi, rank, world, group, device)
+    if getattr(ops, "msg_records", 0) and int(table[:, :2].max()) <= ops.msg_records:    # same table, same answer on every rank
+        recv_lo, recv_hi = ops.exchange(send_lo, send_hi, n_from_lo, n_from_hi)
+    else:
+        recv_lo, recv_hi = _payload_exchange(send_lo, send_hi, n_from_lo, n_from_hi, rank, world, group, device)
     _mark("p2p", device)
     ops.refill(n, n_new, torch.cat([recv_lo, recv_hi]))
     _mark("refill", device)
@@ -407,6 +431,8 @@ class SlabSimulator:
         if os.environ.get("MPMK_MG_PEER", "1") != "0":
             self._open_peer_halo(planes)
         self._ops = CudaRecordOps(b, _stream)
+        if self.halo_path == "peer" and os.environ.get("MPMK_MG_LL_MIGRATE", "1") != "0":
+            self._ops.msg_records = self._msg_records     # the payload travels as flagged stores over NVLink (mpmk_mg_ll_send)
         self._auto = migrate_every in (None, 0, "auto")
         self.max_interval = 64
         self._dt = float(args.substep_dt)
@@ -439,7 +465,11 @@ class SlabSimulator:
         hbuf = (C.c_char * 64)()
         ok = 1
         try:
-            b.ctx.call("mpmk_mg_peer_alloc", planes * self.n_grid * self.n_grid * 16, C.cast(hbuf, C.c_void_p), 64)
+            # message slots for the migration payload: 1/32 of a rank's share per neighbour and migration (a migration
+            # that moves more goes through NCCL instead), LL-encoded = 8 bytes per 4-byte word
+            self._msg_records = max(32768, (self.n_global // self.world) // 32)
+            msg_bytes = ((self._msg_records * RECORD_WIDTH + 1) // 2) * 16
+            b.ctx.call("mpmk_mg_peer_alloc_ex", planes * self.n_grid * self.n_grid * 16, msg_bytes, C.cast(hbuf, C.c_void_p), 64)
         except _native.MpmkError:
             ok = 0
         mine = torch.frombuffer(bytearray(hbuf.raw), dtype=torch.uint8).clone().to(self.device)

@@ -274,6 +274,16 @@ MPMK_API int mpmk_mg_close_holes(mpmk_ctx* ctx, const void* holes_dev, int64_t n
  * there (st.release.sys), and one kernel that waits for the neighbours' flags and adds what they pushed -- no NCCL
  * call on the substep path.  buf_bytes >= (2*ghost+2) * n_grid^2 * 16 covers any row range.                     */
 MPMK_API int mpmk_mg_peer_alloc(mpmk_ctx* ctx, int64_t buf_bytes, void* handle_out, int handle_bytes);
+/* the same with 2 x 2 message slots of msg_bytes each behind the halo slots (mpmk_mg_ll_send / _recv)           */
+MPMK_API int mpmk_mg_peer_alloc_ex(mpmk_ctx* ctx, int64_t buf_bytes, int64_t msg_bytes, void* handle_out, int handle_bytes);
+/* Flagged message to / from a neighbour through the mapped exchange blocks (the migration payload of
+ * mpm_solver/slabs.py; replaces ncclSend / ncclRecv there).  n_words 32-bit words travel as 16-byte stores
+ * {w0, tag, w1, tag} over NVLink into slot [side][tag & 1]; the receiver spins until the tags match: no collective,
+ * no fence, nothing on the host.  side 0 = rank-1, 1 = rank+1.  tag != 0, different from the previous message's tag
+ * through the same slot, same on both sides.  A receive that times out (4 s) sets the error word mpmk_mg_peer_error
+ * and mpmk_mg_scan report.  No reference counterpart.                                                          */
+MPMK_API int mpmk_mg_ll_send(mpmk_ctx* ctx, int side, const void* src_dev, int64_t n_words, uint32_t tag, void* stream);
+MPMK_API int mpmk_mg_ll_recv(mpmk_ctx* ctx, int side, void* dst_dev, int64_t n_words, uint32_t tag, void* stream);
 MPMK_API int mpmk_mg_peer_open(mpmk_ctx* ctx, const void* handle_lo, const void* handle_hi);
 MPMK_API int mpmk_mg_peer_enabled(mpmk_ctx* ctx);
 /* unmap / free the exchange blocks and return to the NCCL halo path */
