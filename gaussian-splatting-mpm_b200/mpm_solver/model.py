@@ -112,6 +112,20 @@ class _Backend:
         self.export_fresh = False
         self.cov_from_postprocess = False
 
+    def read_small(self, t):
+        """a small device tensor on the host without a copy engine (mpmk_read_small: a kernel stores it into pinned host
+        memory).  `.item()` / `.cpu()` queue on the device-to-host copy engine behind whatever bulk download the caller
+        has in flight on another stream -- a frame loop that streams its results out then stalls here for the rest of
+        that download (measured: 3 of 4.3 ms per frame at 2 GPUs, 10 of 12.8 ms at 8)."""
+        if t.dtype == torch.bool:
+            t = t.to(torch.int32)
+        t = t.contiguous()
+        words = (t.numel() * t.element_size() + 3) // 4
+        if getattr(self, "_pin", None) is None or self._pin.numel() < words:
+            self._pin = torch.empty(max(words, 1024), dtype=torch.int32).pin_memory()
+        self.ctx.call("mpmk_read_small", self._pin.data_ptr(), t.data_ptr(), words, _stream())
+        return self._pin[:words].clone().view(t.dtype)[: t.numel()].reshape(t.shape)
+
     def mark_stress_dirty(self, f_written=False, ys_written=False):
         """a write the constitutive update depends on (mu, lam, material, yield_stress, F, the scalar model
         parameters): redo the update before the next substep, from the stored F_trial / pre-return-map yield stress

@@ -144,10 +144,10 @@ def _base_xy_i32(keys: torch.Tensor, nt: int):
     return bx, by
 
 
-def _payload_exchange(send_lo, send_hi, n_from_lo, n_from_hi, rank, world, group, device):
+def _payload_exchange(send_lo, send_hi, n_from_lo, n_from_hi, rank, world, group, device, width=RECORD_WIDTH):
     """leavers to rank-1 / rank+1, arrivals from them; the counts are already known on every rank"""
-    recv_lo = torch.empty((n_from_lo, RECORD_WIDTH), dtype=torch.int32, device=device)
-    recv_hi = torch.empty((n_from_hi, RECORD_WIDTH), dtype=torch.int32, device=device)
+    recv_lo = torch.empty((n_from_lo, width), dtype=torch.int32, device=device)
+    recv_hi = torch.empty((n_from_hi, width), dtype=torch.int32, device=device)
     ops = []
     for peer, snd, rcv in ((rank - 1, send_lo, recv_lo), (rank + 1, send_hi, recv_hi)):
         if not 0 <= peer < world:
@@ -229,14 +229,14 @@ class CudaRecordOps:
         return self.stats[:SCAN_WIDTH].to(torch.int64)
 
     def to_host(self, t):
-        """a small device tensor on the host without a copy engine (mpmk_read_small): `.cpu()` would queue behind any bulk
-        download the caller has in flight on another stream -- a frame loop that streams its results out"""
-        t = t.contiguous()
-        words = t.numel() * t.element_size() // 4
-        if getattr(self, "_pin", None) is None or self._pin.numel() < words:
-            self._pin = torch.empty(max(words, 1024), dtype=torch.int32).pin_memory()
-        self.b.ctx.call("mpmk_read_small", self._pin.data_ptr(), t.data_ptr(), words, self._stream())
-        return self._pin[:words].clone().view(t.dtype).reshape(t.shape)
+        """a small device tensor on the host without a copy engine (model.py: _Backend.read_small)"""
+        return self.b.read_small(t)
+
+    # Sigma_0 (export only; an original-order table indexed by global id) travels with the particle: six more words behind
+    # the record.  Every rank then only ever needs the rows of the particles it holds -- no replication of the whole table
+    # at load time (an all_reduce of 24 B x N_global per reload: 793 MB at 33 M particles).
+    EXTRA = 6
+    ID_WORD = 4 * RECORD_ARRAYS.index("meta")
 
     def pack_leavers(self, n_lo, n_hi):
         self.n_lo, self.n_hi = n_lo, n_hi
@@ -244,6 +244,9 @@ class CudaRecordOps:
         for idx, cnt in ((self.idx_lo, n_lo), (self.idx_hi, n_hi)):
             rows = torch.empty((cnt, RECORD_WIDTH), dtype=torch.int32, device=self.device)
             self.b.ctx.call("mpmk_mg_pack", idx.data_ptr(), cnt, rows.data_ptr(), self._stream())
+            if self.b.ids_init is not None:
+                cov0 = self.b.init_cov[rows[:, self.ID_WORD].long()].view(torch.int32)
+                rows = torch.cat([rows, cov0], dim=1)
             out.append(rows)
         return out
 
@@ -255,8 +258,8 @@ class CudaRecordOps:
         both sends, then both receives, all on the simulator's stream; every rank takes this path for a given migration
         or none does (the caller decides from the all-gathered table); the tag is the migration count"""
         call, st = self.b.ctx.call, self._stream()
-        recv_lo = torch.empty((n_from_lo, RECORD_WIDTH), dtype=torch.int32, device=self.device)
-        recv_hi = torch.empty((n_from_hi, RECORD_WIDTH), dtype=torch.int32, device=self.device)
+        recv_lo = torch.empty((n_from_lo, self.width), dtype=torch.int32, device=self.device)
+        recv_hi = torch.empty((n_from_hi, self.width), dtype=torch.int32, device=self.device)
         for side, snd in ((0, send_lo), (1, send_hi)):
             if snd.shape[0]:
                 snd = snd.contiguous()
@@ -266,8 +269,16 @@ class CudaRecordOps:
                 call("mpmk_mg_ll_recv", side, rcv.data_ptr(), rcv.numel(), self._tag, st)
         return recv_lo, recv_hi
 
+    @property
+    def width(self):
+        """words per travelling record"""
+        return RECORD_WIDTH + (self.EXTRA if self.b.ids_init is not None else 0)
+
     def refill(self, n, n_new, arrivals):
         call, st = self.b.ctx.call, self._stream()
+        if arrivals.shape[1] > RECORD_WIDTH:     # Sigma_0 of the arrivals -> this rank's rows of the table
+            self.b.init_cov[arrivals[:, self.ID_WORD].long()] = arrivals[:, RECORD_WIDTH:].contiguous().view(torch.float32)
+            arrivals = arrivals[:, :RECORD_WIDTH]
         L, R = self.n_lo + self.n_hi, int(arrivals.shape[0])
         holes = torch.cat([self.idx_lo[: self.n_lo], self.idx_hi[: self.n_hi]])
         arrivals = arrivals.contiguous()
@@ -342,7 +353,8 @@ def migrate(store: dict, n: int, capacity: int, bounds, rank: int, ghost: int, n
     if getattr(ops, "msg_records", 0) and int(table[:, :2].max()) <= ops.msg_records:    # same table, same answer on every rank
         recv_lo, recv_hi = ops.exchange(send_lo, send_hi, n_from_lo, n_from_hi)
     else:
-        recv_lo, recv_hi = _payload_exchange(send_lo, send_hi, n_from_lo, n_from_hi, rank, world, group, device)
+        recv_lo, recv_hi = _payload_exchange(send_lo, send_hi, n_from_lo, n_from_hi, rank, world, group, device,
+                                             width=getattr(ops, "width", RECORD_WIDTH))
     _mark("p2p", device)
     ops.refill(n, n_new, torch.cat([recv_lo, recv_hi]))
     _mark("refill", device)
@@ -440,7 +452,6 @@ class SlabSimulator:
             self.migrate_every = 1   # until the first migration has measured the speeds
         self.stats = {"migrations": 0, "sent": 0, "received": 0}
         self._since_migration = 0
-        self._replicate_init_cov()
         self._warm_up_p2p()
         self._set_slab()
 
@@ -468,7 +479,7 @@ class SlabSimulator:
             # message slots for the migration payload: 1/32 of a rank's share per neighbour and migration (a migration
             # that moves more goes through NCCL instead), LL-encoded = 8 bytes per 4-byte word
             self._msg_records = max(32768, (self.n_global // self.world) // 32)
-            msg_bytes = ((self._msg_records * RECORD_WIDTH + 1) // 2) * 16
+            msg_bytes = ((self._msg_records * (RECORD_WIDTH + CudaRecordOps.EXTRA) + 1) // 2) * 16
             b.ctx.call("mpmk_mg_peer_alloc_ex", planes * self.n_grid * self.n_grid * 16, msg_bytes, C.cast(hbuf, C.c_void_p), 64)
         except _native.MpmkError:
             ok = 0
@@ -507,11 +518,6 @@ class SlabSimulator:
         dx = self.sim.mpm_model.dx
         per_substep = max(vmax * self._dt / dx, 1e-9)
         self.migrate_every = int(max(1, min(self.max_interval, 0.5 * self.ghost / per_substep)))
-
-    def _replicate_init_cov(self):
-        """export needs Sigma_0 of whatever particle a rank holds after migrations: every rank wrote the rows
-        of its own ids (zeros elsewhere), the sum makes the table complete on all ranks"""
-        dist.all_reduce(self.backend.init_cov, group=self.group)
 
     def _set_slab(self, rows=None, zs=None):
         b = self.backend
@@ -552,9 +558,7 @@ class SlabSimulator:
         b.n = n
         self.sim.n_particles = n
         b.ids_init = ids.to(device=self.device, dtype=torch.int32)
-        b.init_cov.zero_()
         self.sim.mpm_state._init_particles(xyz, cov, vol)
-        self._replicate_init_cov()
         self.sim.mpm_model._reinit_packed()
         b.cur["vv"][:n, :3] = vel.to(device=self.device, dtype=torch.float32)
         self.sim.time = 0.0

@@ -100,7 +100,7 @@ class MPM_Simulator(FittingMixin):
     # -- flags / parameters ------------------------------------------------------------------
     def _has_plastic(self):
         mat = self._backend.cur["meta"][: self.n_particles, 1]
-        return bool((mat != 0).any().item()) if self.n_particles else False
+        return bool(int(self._backend.read_small((mat != 0).any().reshape(1))[0])) if self.n_particles else False
 
     def _sync_flags(self):
         f = 0
