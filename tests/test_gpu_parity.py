@@ -371,3 +371,29 @@ def test_lego_shaped_config_parity(cuda_dev):
     assert rel_fro(st.particle_F_trial.to_torch().cpu().numpy(), o.in_original_order("particle_F_trial")) < 1e-4
     assert rel_fro(st.particle_cov.to_torch().cpu().numpy(), o.in_original_order("particle_cov")) < 1e-4
     assert abs(g.time - o.time) < 1e-12
+
+
+def test_read_small_matches_cpu_copy(cuda_dev):
+    """mpmk_read_small (a kernel stores a few words into pinned host memory; include/mpmk.h): same values as .cpu() for the
+    shapes the frame path reads back -- a bool flag, the int64 migration table, an odd number of int32 words -- and still right
+    while a bulk download is in flight on another stream (the case it exists for)."""
+    import torch
+    cloud = synthetic.make_cloud(16, 2.0, (4, 4, 4), (4, 4, 4), seed=1)
+    args = synthetic.sim_args(n_grid=16, material="jelly")
+    g = make_gpu(cloud, args, cuda_dev)
+    b = g._backend
+    gen = torch.Generator(device="cpu").manual_seed(5)
+    for t in (torch.tensor([True], device=cuda_dev), torch.randint(-2**40, 2**40, (8, 9), generator=gen).to(cuda_dev),
+              torch.arange(7, dtype=torch.int32, device=cuda_dev), torch.rand(3, generator=gen).to(cuda_dev)):
+        got = b.read_small(t)
+        want = t.to(torch.int32).cpu() if t.dtype == torch.bool else t.cpu()
+        assert got.dtype == want.dtype and got.shape == want.shape and torch.equal(got, want)
+    big_d = torch.zeros(1 << 26, dtype=torch.float32, device=cuda_dev)
+    big_h = torch.empty(1 << 26, dtype=torch.float32).pin_memory()
+    side = torch.cuda.Stream(device=cuda_dev)
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        big_h.copy_(big_d, non_blocking=True)
+    t = torch.arange(100, dtype=torch.int64, device=cuda_dev) * 3
+    assert torch.equal(b.read_small(t), t.cpu())
+    torch.cuda.synchronize()
