@@ -74,3 +74,53 @@ def test_headless_frame_loop(cuda_dev, tmp_path):
     assert np.array_equal(dumped["xyz"][~inside], xyz[~inside]) and np.array_equal(dumped["rotation"], g["rotation"])
     moved = np.abs(dumped["xyz"][inside] - xyz[inside]).max(axis=1)
     assert 0.0 < np.median(moved) < 0.5                                # gravity -100 for 0.02 s: centimetres, not metres
+
+
+def test_orbit_camera_matrices():
+    """render.orbit_camera (main.py:84-106 modify_cam): the camera sits on the sphere at the stated azimuth / elevation,
+    looks at the centre (which projects to the middle of the frame at depth = radius), keeps the frame's vertical axis
+    up on screen, and has a right-handed (right, down, forward) basis"""
+    import render as R
+    centre = np.array([0.3, -0.2, 0.5])
+    frame = np.eye(3)
+    cam = R.orbit_camera(centre, frame, torch.device("cpu"), azimuth=130.0, elevation=10.0, radius=5.75, width=320, height=240, fov_x=0.8, fov_y=0.6)
+    eye = cam.cam_center.numpy().astype(np.float64)
+    d = eye - centre
+    assert abs(np.linalg.norm(d) - 5.75) < 1e-5
+    assert abs(np.degrees(np.arcsin(d[2] / 5.75)) - 10.0) < 1e-4 and abs(np.degrees(np.arctan2(d[1], d[0])) - 130.0) < 1e-4
+    V = cam.view_mat.numpy().T.astype(np.float64)                      # world -> camera (stored transposed, as the rasteriser wants)
+    Rw = V[:3, :3]
+    assert np.allclose(Rw @ Rw.T, np.eye(3), atol=1e-6) and abs(np.linalg.det(Rw) - 1.0) < 1e-6
+    pc = V @ np.append(centre, 1.0)
+    assert np.allclose(pc[:2], 0.0, atol=1e-5) and abs(pc[2] - 5.75) < 1e-5          # on the optical axis, in front
+    up = V @ np.append(centre + np.array([0.0, 0.0, 1.0]), 1.0)
+    assert up[1] < -0.5 and abs(up[0]) < 1e-5                                          # world up = image up (y points down)
+    clip = np.append(centre, 1.0) @ cam.full_proj_mat.numpy().astype(np.float64)      # row vector x (view^T proj^T)
+    ndc = clip[:3] / clip[3]
+    assert np.allclose(ndc[:2], 0.0, atol=1e-5) and 0.0 < ndc[2] < 1.0
+    side = np.append(centre, 1.0) + np.append(Rw[0] * 5.75 * np.tan(0.4), 0.0)         # a point on the right edge of the frustum
+    c2 = side @ cam.full_proj_mat.numpy().astype(np.float64)
+    assert abs(c2[0] / c2[3] - 1.0) < 1e-4
+
+
+@pytest.mark.gpu
+def test_frame_loop_renders_with_unchanged_rasterizer(cuda_dev, tmp_path):
+    """simulate(..., render=True): every frame goes export_world -> the reference's unchanged rasteriser -> PNG; the falling
+    blob is in view and the picture changes from frame to frame"""
+    import render as R
+    try:
+        R.load_rasterizer()
+    except RuntimeError as e:
+        pytest.skip(str(e))
+    import simulate
+    from arguments import from_config
+    from PIL import Image
+    cfg = json.load(open(os.path.join(PKG, "configs", "lego_shape.json")))
+    m, s, r = from_config(cfg, ["--num_frames", "3", "--output_path", str(tmp_path)])
+    solver, means3D, cov3D, log = simulate.simulate(m, s, r, synthetic_n=20000, quiet=True, render=True)
+    b = solver._backend
+    assert means3D.data_ptr() == b.world_xyz.data_ptr() and cov3D.data_ptr() == b.world_cov.data_ptr()     # zero-copy hand-off
+    frames = [np.asarray(Image.open(os.path.join(str(tmp_path), "images", f"{i:04d}.png")), dtype=np.int32) for i in (1, 2, 3)]
+    assert all(f.shape == (800, 800, 3) for f in frames)
+    assert all((f.max(2) > 12).mean() > 0.01 for f in frames)                          # something is on screen
+    assert np.abs(frames[2] - frames[0]).max() > 8                                     # and it moves
