@@ -176,3 +176,53 @@ extern "C" int mpmk_particle_volume(mpmk_ctx* ctx, int64_t n, const void* pos, f
     MPMK_LAUNCH_CHECK(ctx);
     return 0;
 }
+
+// ---- mpmk_particle_volume_noalloc: the same two kernels with the cell-count scratch inside the library ---------------
+// No counterpart in the reference; added for callers that cannot allocate (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The scratch is a file-scope device
+// array of a stated maximum size -- every GPU that loads the library holds these 8 MiB until the process exits -- and the
+// entry point calls no cudaMalloc / cudaFree / allocating library routine.  All calls share the array and it keeps the
+// last call's contents: it is cleared on `stream` before the count, and two calls that overlap on the GPU (different
+// streams, no ordering between them) race.
+#define MPMK_VOL_NOALLOC_MAX_GRID 128   // cells per edge: 128^3 int32 = 8 MiB (the reference's configs use 50^3 and 100^3)
+static __device__ __align__(256) int g_vol_cells[MPMK_VOL_NOALLOC_MAX_GRID * MPMK_VOL_NOALLOC_MAX_GRID * MPMK_VOL_NOALLOC_MAX_GRID];
+
+// In host code `g_vol_cells` is a host-side stand-in, not a device address: the address a kernel can use comes from
+// cudaGetSymbolAddress, looked up once per device with that device current.
+#define MPMK_NOALLOC_MAX_DEVICES 64
+static int* g_vol_cells_addr[MPMK_NOALLOC_MAX_DEVICES];
+
+static int vol_cells_for_device(mpmk_ctx* ctx, int** out) {
+    int cur = -1;
+    MPMK_CHECK(ctx, cudaGetDevice(&cur));
+    if (cur != ctx->device) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_particle_volume_noalloc: device %d is current, the context lives on device %d", cur, ctx->device);
+    if (cur < 0 || cur >= MPMK_NOALLOC_MAX_DEVICES) MPMK_FAIL(ctx, MPMK_ERR_INVALID, "mpmk_particle_volume_noalloc: device ordinal %d beyond %d", cur, MPMK_NOALLOC_MAX_DEVICES);
+    if (!g_vol_cells_addr[cur]) {
+        int* p = nullptr;
+        MPMK_CHECK(ctx, cudaGetSymbolAddress((void**)&p, g_vol_cells));
+        if (!p) MPMK_FAIL(ctx, MPMK_ERR_STATE, "mpmk_particle_volume_noalloc: cudaGetSymbolAddress returned no address");
+        g_vol_cells_addr[cur] = p;
+    }
+    *out = g_vol_cells_addr[cur];
+    return 0;
+}
+
+extern "C" int mpmk_particle_volume_noalloc(mpmk_ctx* ctx, int64_t n, const void* pos, float grid_dx, void* vol, void* stream) {
+    if (!ctx) return MPMK_ERR_STATE;
+    if (n < 0 || (n > 0 && (!pos || !vol))) MPMK_FAIL(ctx, MPMK_ERR_INVALID, "mpmk_particle_volume_noalloc: bad arguments");
+    if (ctx->n_grid > MPMK_VOL_NOALLOC_MAX_GRID)
+        MPMK_FAIL(ctx, MPMK_ERR_INVALID, "mpmk_particle_volume_noalloc: n_grid = %d exceeds the built-in scratch (max %d cells per edge); use mpmk_particle_volume with a caller-provided cell_count buffer",
+                  ctx->n_grid, MPMK_VOL_NOALLOC_MAX_GRID);
+    if (n == 0) return 0;
+    int* cells = nullptr;
+    const int rc = vol_cells_for_device(ctx, &cells);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t n_cells = (size_t)ctx->n_grid * ctx->n_grid * ctx->n_grid;
+    MPMK_CHECK(ctx, cudaMemsetAsync(cells, 0, n_cells * sizeof(int), s));   // the array still holds the last call's counts
+    k_vol_count<<<div_up(n, 256), 256, 0, s>>>((const float*)pos, n, grid_dx, ctx->n_grid, cells);
+    MPMK_LAUNCH_CHECK(ctx);
+    k_vol<<<div_up(n, 256), 256, 0, s>>>((const float*)pos, n, grid_dx, ctx->n_grid, cells, (float*)vol);
+    MPMK_LAUNCH_CHECK(ctx);
+    return 0;
+}

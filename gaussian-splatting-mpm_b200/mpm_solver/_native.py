@@ -104,6 +104,7 @@ def lib():
         "mpmk_count": (i64, [vp]),
         "mpmk_compute_mu_lam": (i, [vp, i64, vp, vp, vp, vp, vp]),
         "mpmk_particle_volume": (i, [vp, i64, vp, f, vp, vp, vp]),
+        "mpmk_particle_volume_noalloc": (i, [vp, i64, vp, f, vp, vp]),
         "mpmk_compute_keys": (i, [vp, vp]),
         "mpmk_constitutive": (i, [vp, f, vp]),
         "mpmk_constitutive_ex": (i, [vp, f, i, i, vp]),

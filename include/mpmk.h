@@ -156,6 +156,17 @@ MPMK_API int mpmk_compute_mu_lam(mpmk_ctx* ctx, int64_t n, const void* logE_dev,
 /* internel_filling/filling.py:12-24; cell_count_dev = int32[n_grid^3] scratch, zeroed by the caller */
 MPMK_API int mpmk_particle_volume(mpmk_ctx* ctx, int64_t n, const void* pos_dev /* float[n][3] */, float grid_dx,
                          void* cell_count_dev, void* vol_dev, void* stream);
+/* mpmk_particle_volume without a caller-provided scratch and without any allocation.  No counterpart in the reference:
+ * added for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  The per-cell counts live in a file-scope device array inside the
+ * library (csrc/export.cu: 128^3 int32 = 8 MiB, held by every GPU that loads the library until the process exits), so
+ * n_grid must be <= 128: larger grids are rejected with MPMK_ERR_INVALID and a message naming the limit.  The context's
+ * device must be current.  The call clears the cells it uses on `stream` and launches the same two kernels as
+ * mpmk_particle_volume: same result, bit for bit.  It calls no cudaMalloc / cudaFree / allocating library routine; the
+ * first call on a device resolves the array's address (cudaGetSymbolAddress).  Every call on a device shares the array:
+ * calls that overlap on the GPU (different streams without an ordering between them) race.                       */
+MPMK_API int mpmk_particle_volume_noalloc(mpmk_ctx* ctx, int64_t n, const void* pos_dev /* float[n][3] */, float grid_dx,
+                                          void* vol_dev, void* stream);
 /* cell keys of the current set from positions (utils.py:94-95 base cell) */
 MPMK_API int mpmk_compute_keys(mpmk_ctx* ctx, void* stream);
 /* utils.py:14-54 compute_stress_from_F_trial on the current set, in place:
