@@ -192,6 +192,11 @@ class TorchRecordOps:
         self.idx_hi = torch.nonzero_static(self.hi_mask, size=n_hi).flatten()
         return pack_records(self.store, self.idx_lo), pack_records(self.store, self.idx_hi)
 
+    def pack_idx(self, idx):
+        """records at the given slots, in that order; the slots become the holes the next refill() fills"""
+        self.idx_lo, self.idx_hi = idx.to(torch.int64), torch.zeros(0, dtype=torch.int64, device=self.device)
+        return pack_records(self.store, self.idx_lo)
+
     def refill(self, n, n_new, arrivals):
         store, device = self.store, self.device
         holes = torch.cat([self.idx_lo, self.idx_hi])
@@ -249,6 +254,12 @@ class CudaRecordOps:
                 rows = torch.cat([rows, cov0], dim=1)
             out.append(rows)
         return out
+
+    def pack_idx(self, idx):
+        """records (+ Sigma_0) at the given slots, in that order; the slots become the holes the next refill() fills"""
+        cnt = int(idx.numel())
+        self.idx_lo[:cnt] = idx.to(torch.int32)
+        return self.pack_leavers(cnt, 0)[0]
 
     msg_records = 0   # > 0: neighbours' exchange blocks are mapped with message slots for that many records
     _tag = 0
@@ -359,6 +370,57 @@ def migrate(store: dict, n: int, capacity: int, bounds, rank: int, ghost: int, n
     ops.refill(n, n_new, torch.cat([recv_lo, recv_hi]))
     _mark("refill", device)
     return n_new, stats
+
+
+def recut(store: dict, n: int, capacity: int, rank: int, world: int, ghost: int, nt: int, n_grid: int, group=None, ops=None,
+          align: int = 4):
+    """New slab cuts at particle-count quantiles of the CURRENT cloud (a scene that collapses or
+    spreads starves equal-width slabs), and every particle to the rank that owns its base-cell plane under them.
+    Unlike migrate() a particle may have to cross several ranks, so the records travel in one all_to_all; between
+    re-cuts the cheap neighbour migration keeps ownership.  Collective; two host synchronisations (the global plane
+    histogram, the count matrix).  Returns (n_new, new_bounds, stats)."""
+    device = store["keys"].device
+    if ops is None:
+        ops = TorchRecordOps(store, nt, n_grid)
+    rd = ops.to_host if hasattr(ops, "to_host") else (lambda t: t.cpu())
+    bx = _base_xy_i32(store["keys"][:n], nt)[0].to(torch.int64) if n > 0 else torch.zeros(0, dtype=torch.int64, device=device)
+    hist = torch.bincount(bx, minlength=n_grid)[:n_grid].to(torch.int64)
+    if world > 1:
+        dist.all_reduce(hist, group=group)
+    bounds = quantile_bounds(rd(hist), world, align=align, min_width=max(2 * ghost + 2, 2 * align))
+    check_bounds(bounds, ghost)
+    cuts = torch.tensor(bounds[1:-1], dtype=torch.int64, device=device)
+    dest = torch.searchsorted(cuts, bx, right=True)                   # plane b belongs to slab r iff bounds[r] <= b < bounds[r+1]
+    idx = torch.nonzero(dest != rank).flatten()
+    order = torch.argsort(dest[idx], stable=True)                     # grouped by destination rank, slot order inside a group
+    idx = idx[order]
+    counts = torch.cat([torch.bincount(dest[idx], minlength=world).to(torch.int64),
+                        torch.tensor([n, capacity], dtype=torch.int64, device=device)])
+    table = torch.empty(world * (world + 2), dtype=torch.int64, device=device)
+    if world > 1:
+        dist.all_gather_into_tensor(table, counts.contiguous(), group=group)
+    else:
+        table[: world + 2] = counts
+    table = rd(table).view(world, world + 2)                          # table[src, dst], then the source's count and capacity
+    send = [int(c) for c in table[rank, :world]]
+    recv = [int(table[r, rank]) for r in range(world)]
+    n_new = n - sum(send) + sum(recv)
+    stats = {"sent": sum(send), "received": sum(recv), "bounds": bounds}
+    # collective: every rank sees the same table, every rank raises (one rank leaving alone would hang the others' all_to_all)
+    after = [int(table[r, world]) - int(table[r, :world].sum()) + int(table[:, r].sum()) for r in range(world)]
+    over = [r for r in range(world) if after[r] > int(table[r, world + 1])]
+    if over:
+        raise SlabError(f"ranks {over}: {[after[r] for r in over]} particles after the re-cut exceed the capacities "
+                        f"{[int(table[r, world + 1]) for r in over]} (construct the SlabSimulator with a larger capacity)")
+    table = table[:, :world]
+    if int(table.sum()) == 0:
+        return n, bounds, stats
+    rows = ops.pack_idx(idx)
+    arrivals = torch.empty((sum(recv), rows.shape[1]), dtype=torch.int32, device=device)
+    if world > 1:
+        dist.all_to_all_single(arrivals, rows.contiguous(), output_split_sizes=recv, input_split_sizes=send, group=group)
+    ops.refill(n, n_new, arrivals)
+    return n_new, bounds, stats
 
 
 def global_row_range(store: dict, n: int, nt: int, n_grid: int, margin: int, group=None, axis="y", to_host=None):
@@ -547,6 +609,34 @@ class SlabSimulator:
         self._set_slab(st["rows"], st["zs"])
         _mark("set_slab", self.device)
         return st
+
+    def recut(self):
+        """re-balance: new cuts at particle-count quantiles of the current cloud, every particle to its new owner (one
+        all_to_all; module-level recut()).  Call it between frames when the counts have drifted apart -- `imbalance()` says
+        by how much; the per-substep work of a rank is proportional to its count, and the halo makes every rank wait for
+        the slowest.  Returns the new bounds."""
+        b = self.backend
+        n_new, bounds, st = recut(self._store(), b.n, b.capacity, self.rank, self.world, self.ghost, self.nt, self.n_grid, self.group,
+                                  ops=self._ops)
+        self.bounds = list(bounds)
+        b.n = n_new
+        self.sim.n_particles = n_new
+        b.ctx.call("mpmk_mg_set_count", n_new)
+        b.invalidate()
+        self.stats["sent"] += st["sent"]
+        self.stats["received"] += st["received"]
+        self.stats["recuts"] = self.stats.get("recuts", 0) + 1
+        self._since_migration = 0
+        self._set_slab()
+        return self.bounds
+
+    def imbalance(self):
+        """max over ranks of the local particle count / the mean count (1.0 = perfectly balanced); collective"""
+        t = torch.tensor([float(self.backend.n)], dtype=torch.float64, device=self.device)
+        counts = [torch.empty_like(t) for _ in range(self.world)]
+        dist.all_gather(counts, t, group=self.group)
+        c = self._ops.to_host(torch.cat(counts))
+        return float(c.max() / max(float(c.mean()), 1.0))
 
     def reload(self, xyz, cov, vol, vel, ids):
         """re-initialise this rank's particles in place from new data (the constructor's state
