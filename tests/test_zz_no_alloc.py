@@ -34,7 +34,8 @@ def _both(ctx, pos, dev):
     alloc0 = torch.cuda.memory_allocated(dev)
     ctx.call("mpmk_particle_volume_noalloc", n, pos.data_ptr(), float(dx), got.data_ptr(), st)
     torch.cuda.synchronize()
-    return got.cpu().numpy(), want.cpu().numpy(), cells.cpu().numpy(), free0 - torch.cuda.mem_get_info(dev)[0], torch.cuda.memory_allocated(dev) - alloc0
+    d_free, d_alloc = free0 - torch.cuda.mem_get_info(dev)[0], torch.cuda.memory_allocated(dev) - alloc0   # before anything else runs
+    return got.cpu().numpy(), want.cpu().numpy(), cells.cpu().numpy(), d_free, d_alloc
 
 
 def test_particle_volume_noalloc_matches_existing_entry_point(cuda_dev):
