@@ -217,3 +217,37 @@ def test_recut_balances_and_keeps_every_record_gloo(world, n_per):
     # balanced up to the granularity of tile-aligned cuts: the uniform cuts started at max / mean of 2.7 .. 3.9
     total = sum(counts)
     assert max(counts) / (total / world) < 1.35, counts
+
+
+def _recut_overflow_worker(rank, world, port, bounds, n_per, caps, n_grid, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        nt = (n_grid + 3) // 4
+        store = _fake_store(rank, bounds, n_per[rank], max(caps), nt, n_grid, 0, seed=29)
+        try:
+            slabs.recut(store, n_per[rank], caps[rank], rank, world, 1, nt, n_grid)
+            q.put((rank, None))
+        except slabs.SlabError as e:
+            q.put((rank, str(e)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_recut_capacity_overflow_raises_on_every_rank():
+    """rank 1 cannot take its re-balanced share: BOTH ranks raise (from the all-gathered table) before any record moves --
+    a rank leaving alone would hang the other in the all_to_all"""
+    n_grid, world = 128, 2
+    bounds = slabs.uniform_bounds(n_grid, 8, 120, world)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 33500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_recut_overflow_worker, args=(r, world, port, bounds, [9000, 200], [16384, 1024], n_grid, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=90) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(res[r] is not None and "ranks [1]" in res[r] and "capacit" in res[r] for r in range(world)), res
